@@ -1,0 +1,131 @@
+/*
+ * b200km.h - C ABI of the B200-native KMeans (Lloyd fit / predict) backend.
+ *
+ * This is the thin layer the Python plugin slots call in place of cuML's KMeansMG.  The
+ * reference has no C interface for this path: its fit-function slot and transform slot are
+ * Python closures that call into cuML (reference: python/src/spark_rapids_ml/clustering.py:348-386
+ * and :466-499) and its communicator is created by python/src/spark_rapids_ml/common/
+ * cuml_context.py:35-167.  Every entry point below names the reference call site it replaces.
+ *
+ * Conventions
+ *  - every function returns 0 on success, non-zero on failure; b200km_last_error() then returns a
+ *    thread-local, NUL-terminated message.  No C++ exception crosses this boundary.
+ *  - handles are opaque, one per (process, GPU), not thread-safe.
+ *  - all `const float* X`, centroid, label and accumulator pointers are DEVICE pointers owned by
+ *    the caller (e.g. torch tensors' data_ptr()); scalars returned through `double*`/`int*`
+ *    marked "host" are written to host memory after the stream has been synchronised.
+ *  - `stream` is a cudaStream_t passed as void* (0 = the legacy default stream).  All work is
+ *    enqueued on it.
+ *  - X is row-major [n, d] float32, centroids row-major [k, d] float32, labels int32.
+ *  - the library allocates only its own workspace (cudaMalloc at first use, grown on demand and
+ *    released by b200km_destroy).
+ */
+#ifndef B200KM_H_
+#define B200KM_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct b200km_handle b200km_handle;
+
+#define B200KM_UNIQUE_ID_BYTES 128
+
+/* kernel path selectors for b200km_set_path (diagnostics / tests) */
+#define B200KM_PATH_AUTO 0
+#define B200KM_PATH_FFMA 1 /* generic SIMT FFMA tiles + separate update pass */
+#define B200KM_PATH_TC 2   /* tcgen05/TMEM/TMA 3xTF32 fused pass (where the shape allows) */
+
+/* init modes for b200km_init_centroids; reference: clustering.py:72 ("initMode" -> "init"),
+ * values "random" and "k-means||" (clustering.py:185-186, tests/test_kmeans.py:84,93). */
+#define B200KM_INIT_RANDOM 0
+#define B200KM_INIT_KMEANS_PARALLEL 1
+
+/* Library version string, e.g. "b200km 0.1.0 (sm_100a)". */
+const char* b200km_version(void);
+
+/* Message for the last failing call on this thread. */
+const char* b200km_last_error(void);
+
+/* Rank 0 creates the 128-byte NCCL unique id that every rank passes to b200km_create.
+ * Replaces `nccl.get_unique_id()` in cuml_context.py:75-77. */
+int b200km_comm_get_unique_id(void* out128);
+
+/* Creates the per-GPU handle: selects `device`, and when nranks > 1 joins the NCCL communicator
+ * (ncclCommInitRank) identified by uid128.  nranks == 1 needs no NCCL and uid128 may be NULL.
+ * Replaces `Handle(n_streams=0)` + `nccl().init(nranks, uid, rank)` +
+ * `inject_comms_on_handle_coll_only` in cuml_context.py:70,116-124. */
+int b200km_create(int device, int rank, int nranks, const void* uid128, b200km_handle** out);
+
+/* Orderly teardown (ncclCommDestroy + workspace free).  Replaces `nccl.destroy()` in
+ * cuml_context.py:155-157. */
+int b200km_destroy(b200km_handle* h);
+
+/* Teardown after a failure on some rank (ncclCommAbort: does not wait for peers).  Replaces
+ * `nccl.abort()` in cuml_context.py:158-159. */
+int b200km_abort(b200km_handle* h);
+
+/* Forces a kernel path (B200KM_PATH_*); AUTO picks per shape.  Asking for a path the shape does
+ * not support makes the next compute call fail rather than fall back. */
+int b200km_set_path(b200km_handle* h, int path);
+
+/* Name of the path the last compute call on this handle used ("ffma" / "tc"). */
+const char* b200km_last_path(b200km_handle* h);
+
+/* Instrumentation for the benchmark.  While enabled, every pass brackets its dominant kernel
+ * (the fused tcgen05 kernel, or the FFMA assignment kernel) with a CUDA event pair on the caller's
+ * stream and the handle counts its kernel launches.  b200km_profile_read waits for the recorded
+ * events, returns the summed kernel time, the number of bracketed launches and the number of all
+ * kernel launches since the last read, and resets the counters.  The reference has only wall-clock
+ * prints for this path (python/benchmark/benchmark/bench_kmeans.py:166-174, utils.py:42-50). */
+int b200km_profile_enable(b200km_handle* h, int on);
+int b200km_profile_read(b200km_handle* h, double* kernel_ms_total, int* kernel_launches,
+                        long long* all_launches);
+
+/* Bytes of library-owned device workspace a fit/predict of this shape needs. */
+int b200km_query_workspace(int64_t n, int d, int k, size_t* bytes_out);
+
+/* Lloyd fit from given initial centroids (identical on all ranks) over this rank's row shard.
+ * Per iteration: nearest-centroid assignment, per-cluster float64 sums/counts, one NCCL sum
+ * all-reduce of [k*d sums | k counts | inertia] when nranks > 1, mean update (empty clusters keep
+ * their centroid), stop when sum_j ||c_new_j - c_old_j||^2 < tol or after max_iter iterations.
+ * centroids_out: device [k,d].  labels_out: device [n_local] or NULL.  inertia_out / n_iter_out:
+ * host scalars or NULL.  inertia is the float64 sum of squared distances of all ranks' rows to
+ * the FINAL centroids (costs one extra assignment pass, skipped when both inertia_out and
+ * labels_out are NULL).
+ * Replaces `KMeansMG(handle, **cuml_params).fit(X, sample_weight=None)` and the read-back of
+ * `cluster_centers_`, `n_iter_`, `inertia_` in clustering.py:355-384. */
+int b200km_fit(b200km_handle* h, const float* X, int64_t n_local, int d, int k,
+               const float* init_centroids, int max_iter, double tol, float* centroids_out,
+               double* inertia_out, int* n_iter_out, int32_t* labels_out, void* stream);
+
+/* One assignment + accumulation pass over this rank's rows (no all-reduce, no update):
+ * sums_out device float64 [k*d], counts_out device float64 [k], inertia_out device float64 [1]
+ * (sum of squared distances to `centroids`), labels_out device int32 [n] or NULL.
+ * Building block of b200km_fit exposed for tests and the benchmark; it is the per-iteration
+ * device work of `KMeansMG.fit` (clustering.py:367-370). */
+int b200km_lloyd_step(b200km_handle* h, const float* X, int64_t n, int d, int k,
+                      const float* centroids, double* sums_out, double* counts_out,
+                      double* inertia_out, int32_t* labels_out, void* stream);
+
+/* Nearest-centroid labels (int32) for n rows; min_dist_out (device float32 [n], squared distance
+ * to the chosen centroid) may be NULL.  No communication.
+ * Replaces `kmeans.predict(df, normalize_weights=False)` in clustering.py:493-497. */
+int b200km_predict(b200km_handle* h, const float* X, int64_t n, int d, const float* centroids,
+                   int k, int32_t* labels_out, float* min_dist_out, void* stream);
+
+/* Chooses k initial centroids from the (row-sharded) data and leaves the same [k,d] array on
+ * every rank in `centroids_out` (device).  mode: B200KM_INIT_RANDOM or
+ * B200KM_INIT_KMEANS_PARALLEL (oversampling = cuML's oversampling_factor, clustering.py:119).
+ * Replaces the `init=` handling inside `KMeansMG.fit` (clustering.py:72,117,355-359). */
+int b200km_init_centroids(b200km_handle* h, const float* X, int64_t n_local, int d, int k,
+                          int mode, uint64_t seed, double oversampling, float* centroids_out,
+                          void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200KM_H_ */

@@ -1,0 +1,521 @@
+// C-ABI layer of b200km (declared in include/b200km.h): handle, workspace, NCCL bring-up, the
+// device-resident Lloyd loop and predict.  No C++ exception and no torch type crosses this file's
+// extern "C" surface.
+#include "../../include/b200km.h"
+#include "common.cuh"
+#include "tc.cuh"
+
+#include <dlfcn.h>
+#include <nccl.h>
+
+#include <algorithm>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <random>
+#include <unordered_set>
+#include <vector>
+
+using namespace b200km;
+
+namespace {
+
+thread_local char g_err[1024] = "";
+
+int fail(const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+    return 1;
+}
+
+#define CU_TRY(expr)                                                                          \
+    do {                                                                                      \
+        cudaError_t _e = (expr);                                                              \
+        if (_e != cudaSuccess)                                                                \
+            return fail("%s failed: %s (%s:%d)", #expr, cudaGetErrorString(_e), __FILE__, __LINE__); \
+    } while (0)
+
+// ---- NCCL through dlopen: the library has no link-time dependency on it, a single-GPU process
+// never loads it, and a process that already holds libnccl.so.2 (torch) shares that copy. --------
+struct NcclApi {
+    void* lib = nullptr;
+    ncclResult_t (*GetUniqueId)(ncclUniqueId*) = nullptr;
+    ncclResult_t (*CommInitRank)(ncclComm_t*, int, ncclUniqueId, int) = nullptr;
+    ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
+    ncclResult_t (*CommAbort)(ncclComm_t) = nullptr;
+    ncclResult_t (*AllReduce)(const void*, void*, size_t, ncclDataType_t, ncclRedOp_t, ncclComm_t,
+                              cudaStream_t) = nullptr;
+    ncclResult_t (*AllGather)(const void*, void*, size_t, ncclDataType_t, ncclComm_t, cudaStream_t) = nullptr;
+    const char* (*GetErrorString)(ncclResult_t) = nullptr;
+};
+NcclApi g_nccl;
+
+int load_nccl() {
+    if (g_nccl.lib) return 0;
+    const char* names[] = {"libnccl.so.2", "libnccl.so"};
+    void* lib = nullptr;
+    for (const char* nm : names) {
+        lib = dlopen(nm, RTLD_NOW | RTLD_GLOBAL);
+        if (lib) break;
+    }
+    if (!lib) return fail("cannot dlopen libnccl.so.2: %s", dlerror());
+#define SYM(field, name)                                                        \
+    *(void**)(&g_nccl.field) = dlsym(lib, name);                                \
+    if (!g_nccl.field) return fail("libnccl has no symbol %s", name);
+    SYM(GetUniqueId, "ncclGetUniqueId")
+    SYM(CommInitRank, "ncclCommInitRank")
+    SYM(CommDestroy, "ncclCommDestroy")
+    SYM(CommAbort, "ncclCommAbort")
+    SYM(AllReduce, "ncclAllReduce")
+    SYM(AllGather, "ncclAllGather")
+    SYM(GetErrorString, "ncclGetErrorString")
+#undef SYM
+    g_nccl.lib = lib;
+    return 0;
+}
+
+#define NCCL_TRY(expr)                                                                              \
+    do {                                                                                            \
+        ncclResult_t _r = (expr);                                                                   \
+        if (_r != ncclSuccess)                                                                      \
+            return fail("%s failed: %s (%s:%d)", #expr, g_nccl.GetErrorString(_r), __FILE__, __LINE__); \
+    } while (0)
+
+constexpr int kRing = 4;  // how many iterations the host may run ahead of the device
+
+}  // namespace
+
+struct b200km_handle {
+    int device = 0, rank = 0, nranks = 1;
+    ncclComm_t comm = nullptr;
+    int path = B200KM_PATH_AUTO;
+    const char* last_path = "none";
+    // workspace
+    IterState* d_state = nullptr;
+    IterState* h_state = nullptr;  // pinned ring [kRing] + 1 slot for the final read
+    double* h_scalar = nullptr;    // pinned
+    cudaEvent_t ev[kRing] = {};
+    double* d_acc = nullptr;
+    size_t acc_cap = 0;
+    double* d_shift = nullptr;
+    float* d_cnorm = nullptr;
+    size_t k_cap = 0;
+    float* d_C = nullptr;
+    size_t kd_cap = 0;
+    float* d_xnorm = nullptr;
+    float* d_best = nullptr;
+    int32_t* d_labels = nullptr;
+    unsigned int* d_work = nullptr;
+    size_t n_cap = 0;
+    TcWorkspace tc;
+    // instrumentation (b200km_profile_*)
+    bool prof = false;
+    static constexpr int kProfMax = 256;
+    cudaEvent_t pev[2 * kProfMax] = {};
+    int prof_n = 0;
+    unsigned long long launches = 0;
+};
+
+namespace {
+
+int free_ws(b200km_handle* h) {
+    cudaFree(h->d_state);
+    cudaFree(h->d_acc);
+    cudaFree(h->d_shift);
+    cudaFree(h->d_cnorm);
+    cudaFree(h->d_C);
+    cudaFree(h->d_xnorm);
+    cudaFree(h->d_best);
+    cudaFree(h->d_labels);
+    cudaFree(h->d_work);
+    tc_free(&h->tc);
+    if (h->h_state) cudaFreeHost(h->h_state);
+    if (h->h_scalar) cudaFreeHost(h->h_scalar);
+    for (auto& e : h->ev)
+        if (e) cudaEventDestroy(e);
+    for (auto& e : h->pev)
+        if (e) cudaEventDestroy(e);
+    return 0;
+}
+
+template <typename T>
+int grow(T** p, size_t* cap, size_t need) {
+    if (need <= *cap && *p) return 0;
+    if (*p) CU_TRY(cudaFree(*p));
+    *p = nullptr;
+    const size_t want = need + need / 8 + 64;
+    CU_TRY(cudaMalloc((void**)p, sizeof(T) * want));
+    *cap = want;
+    return 0;
+}
+
+int ensure_ws(b200km_handle* h, int64_t n, int d, int k, bool need_row_bufs) {
+    const size_t kd = (size_t)k * d;
+    const size_t acc_len = kd + k + 1;
+    if (acc_len > h->acc_cap || !h->d_acc) {
+        if (h->d_acc) CU_TRY(cudaFree(h->d_acc));
+        h->d_acc = nullptr;
+        CU_TRY(cudaMalloc((void**)&h->d_acc, sizeof(double) * (acc_len + 64)));
+        h->acc_cap = acc_len + 64;
+    }
+    if ((size_t)k > h->k_cap || !h->d_cnorm) {
+        if (h->d_cnorm) CU_TRY(cudaFree(h->d_cnorm));
+        if (h->d_shift) CU_TRY(cudaFree(h->d_shift));
+        h->d_cnorm = nullptr;
+        h->d_shift = nullptr;
+        CU_TRY(cudaMalloc((void**)&h->d_cnorm, sizeof(float) * (k + 64)));
+        CU_TRY(cudaMalloc((void**)&h->d_shift, sizeof(double) * (k + 64)));
+        h->k_cap = k + 64;
+    }
+    if (grow(&h->d_C, &h->kd_cap, kd)) return 1;
+    if (need_row_bufs && ((size_t)n > h->n_cap || !h->d_xnorm)) {
+        const size_t want = (size_t)n + (size_t)n / 8 + 256;
+        for (void** p : {(void**)&h->d_xnorm, (void**)&h->d_best, (void**)&h->d_labels, (void**)&h->d_work}) {
+            if (*p) CU_TRY(cudaFree(*p));
+            *p = nullptr;
+            CU_TRY(cudaMalloc(p, 4 * want));
+        }
+        h->n_cap = want;
+    }
+    return 0;
+}
+
+int check_shape(const b200km_handle* h, const void* X, int64_t n, int d, int k) {
+    if (!h) return fail("null handle");
+    if (!X && n > 0) return fail("X is null");
+    if (n < 0 || n >= ((int64_t)1 << 31)) return fail("n=%lld out of range [0, 2^31)", (long long)n);
+    if (d <= 0 || d > (1 << 20)) return fail("d=%d out of range", d);
+    if (k <= 0 || k > (1 << 24)) return fail("k=%d out of range", k);
+    return 0;
+}
+
+// Picks the kernel path for this shape, honouring a forced path (and failing if it cannot run).
+int pick_path(b200km_handle* h, const float* X, int d, int k, bool* use_tc) {
+    const bool can = tc_supported(X, d, k);
+    if (h->path == B200KM_PATH_TC && !can)
+        return fail("tcgen05 path forced but not available for d=%d k=%d (needs d%%4==0, 16B-aligned X, "
+                    "d<=%d, k<=%d)", d, k, tc_max_d(), tc_max_k());
+    *use_tc = (h->path == B200KM_PATH_TC) || (h->path == B200KM_PATH_AUTO && can);
+    h->last_path = *use_tc ? "tc" : "ffma";
+    return 0;
+}
+
+// One assignment (+ optional accumulation) pass on the chosen path.
+// labels/best may be workspace or caller buffers.  acc == nullptr -> assignment only.
+int run_pass(b200km_handle* h, bool use_tc, const float* X, int64_t n, int d, int k, const float* C,
+             int32_t* labels, float* best, double* acc, bool honor_done, cudaStream_t s) {
+    // the dominant kernel of the pass is bracketed by an event pair when profiling is on
+    const bool rec = h->prof && h->prof_n < b200km_handle::kProfMax;
+    if (rec) CU_TRY(cudaEventRecord(h->pev[2 * h->prof_n], s));
+    if (use_tc) {
+        if (tc_pass(&h->tc, X, n, d, k, C, h->d_cnorm, labels, best, acc, h->d_state, honor_done, s))
+            return fail("tcgen05 pass failed: %s", tc_last_error());
+        if (rec) CU_TRY(cudaEventRecord(h->pev[2 * h->prof_n + 1], s));
+        if (rec) h->prof_n++;
+        h->launches += 1;
+        return 0;
+    }
+    launch_assign_ffma(X, n, d, C, k, h->d_cnorm, h->d_xnorm, labels, best, h->d_state, h->d_work, honor_done, s);
+    if (rec) CU_TRY(cudaEventRecord(h->pev[2 * h->prof_n + 1], s));
+    if (rec) h->prof_n++;
+    launch_refine(X, n, d, C, k, labels, best, h->d_state, h->d_work, honor_done, s);
+    if (acc) launch_update(X, n, d, k, labels, best, acc, h->d_state, honor_done, s);
+    h->launches += acc ? 3 : 2;
+    CU_TRY(cudaGetLastError());
+    return 0;
+}
+
+}  // namespace
+
+extern "C" {
+
+const char* b200km_version(void) { return "b200km 0.1.0 (sm_100a)"; }
+
+const char* b200km_last_error(void) { return g_err; }
+
+int b200km_comm_get_unique_id(void* out128) {
+    if (!out128) return fail("out128 is null");
+    if (load_nccl()) return 1;
+    static_assert(sizeof(ncclUniqueId) == B200KM_UNIQUE_ID_BYTES, "NCCL unique id size");
+    ncclUniqueId id;
+    NCCL_TRY(g_nccl.GetUniqueId(&id));
+    memcpy(out128, &id, sizeof(id));
+    return 0;
+}
+
+int b200km_create(int device, int rank, int nranks, const void* uid128, b200km_handle** out) {
+    if (!out) return fail("out is null");
+    *out = nullptr;
+    if (nranks < 1 || rank < 0 || rank >= nranks) return fail("bad rank %d / nranks %d", rank, nranks);
+    int ndev = 0;
+    CU_TRY(cudaGetDeviceCount(&ndev));
+    if (device < 0 || device >= ndev) return fail("device %d not present (%d visible)", device, ndev);
+    CU_TRY(cudaSetDevice(device));
+    cudaDeviceProp prop;
+    CU_TRY(cudaGetDeviceProperties(&prop, device));
+    if (prop.major != 10)
+        return fail("b200km is built for sm_100a only; device %d is sm_%d%d", device, prop.major, prop.minor);
+    b200km_handle* h = new b200km_handle();
+    h->device = device;
+    h->rank = rank;
+    h->nranks = nranks;
+    if (cudaMalloc((void**)&h->d_state, sizeof(IterState)) != cudaSuccess ||
+        cudaMemset(h->d_state, 0, sizeof(IterState)) != cudaSuccess ||
+        cudaMallocHost((void**)&h->h_state, sizeof(IterState) * (kRing + 1)) != cudaSuccess ||
+        cudaMallocHost((void**)&h->h_scalar, sizeof(double) * 8) != cudaSuccess) {
+        free_ws(h);
+        delete h;
+        return fail("handle allocation failed: %s", cudaGetErrorString(cudaGetLastError()));
+    }
+    for (auto& e : h->ev) {
+        if (cudaEventCreateWithFlags(&e, cudaEventDisableTiming) != cudaSuccess) {
+            free_ws(h);
+            delete h;
+            return fail("cudaEventCreate failed");
+        }
+    }
+    if (nranks > 1) {
+        if (!uid128) {
+            free_ws(h);
+            delete h;
+            return fail("uid128 is null with nranks=%d", nranks);
+        }
+        if (load_nccl()) {
+            free_ws(h);
+            delete h;
+            return 1;
+        }
+        ncclUniqueId id;
+        memcpy(&id, uid128, sizeof(id));
+        ncclResult_t r = g_nccl.CommInitRank(&h->comm, nranks, id, rank);
+        if (r != ncclSuccess) {
+            free_ws(h);
+            delete h;
+            return fail("ncclCommInitRank failed: %s", g_nccl.GetErrorString(r));
+        }
+    }
+    *out = h;
+    return 0;
+}
+
+int b200km_destroy(b200km_handle* h) {
+    if (!h) return 0;
+    cudaSetDevice(h->device);
+    if (h->comm) g_nccl.CommDestroy(h->comm);
+    free_ws(h);
+    delete h;
+    return 0;
+}
+
+int b200km_abort(b200km_handle* h) {
+    if (!h) return 0;
+    cudaSetDevice(h->device);
+    if (h->comm) g_nccl.CommAbort(h->comm);
+    free_ws(h);
+    delete h;
+    return 0;
+}
+
+int b200km_set_path(b200km_handle* h, int path) {
+    if (!h) return fail("null handle");
+    if (path < B200KM_PATH_AUTO || path > B200KM_PATH_TC) return fail("unknown path %d", path);
+    h->path = path;
+    return 0;
+}
+
+const char* b200km_last_path(b200km_handle* h) { return h ? h->last_path : "none"; }
+
+int b200km_profile_enable(b200km_handle* h, int on) {
+    if (!h) return fail("null handle");
+    CU_TRY(cudaSetDevice(h->device));
+    if (on && !h->pev[0]) {
+        for (auto& e : h->pev) CU_TRY(cudaEventCreate(&e));
+    }
+    h->prof = on != 0;
+    h->prof_n = 0;
+    h->launches = 0;
+    return 0;
+}
+
+int b200km_profile_read(b200km_handle* h, double* kernel_ms_total, int* kernel_launches, long long* all_launches) {
+    if (!h) return fail("null handle");
+    CU_TRY(cudaSetDevice(h->device));
+    double total = 0.0;
+    for (int i = 0; i < h->prof_n; ++i) {
+        CU_TRY(cudaEventSynchronize(h->pev[2 * i + 1]));
+        float ms = 0.f;
+        CU_TRY(cudaEventElapsedTime(&ms, h->pev[2 * i], h->pev[2 * i + 1]));
+        total += ms;
+    }
+    if (kernel_ms_total) *kernel_ms_total = total;
+    if (kernel_launches) *kernel_launches = h->prof_n;
+    if (all_launches) *all_launches = (long long)h->launches;
+    h->prof_n = 0;
+    h->launches = 0;
+    return 0;
+}
+
+int b200km_query_workspace(int64_t n, int d, int k, size_t* bytes_out) {
+    if (!bytes_out) return fail("bytes_out is null");
+    if (n < 0 || d <= 0 || k <= 0) return fail("bad shape");
+    const size_t kd = (size_t)k * d;
+    size_t b = sizeof(double) * (kd + k + 1 + 64) + sizeof(double) * (k + 64) + sizeof(float) * (k + 64) +
+               sizeof(float) * (kd + kd / 8 + 64) + 16 * ((size_t)n + (size_t)n / 8 + 256) + sizeof(IterState);
+    b += tc_workspace_bytes(d, k);
+    *bytes_out = b;
+    return 0;
+}
+
+int b200km_fit(b200km_handle* h, const float* X, int64_t n_local, int d, int k, const float* init_centroids,
+               int max_iter, double tol, float* centroids_out, double* inertia_out, int* n_iter_out,
+               int32_t* labels_out, void* stream) {
+    if (check_shape(h, X, n_local, d, k)) return 1;
+    if (n_local == 0) return fail("this rank received no rows (every worker needs data)");
+    if (!init_centroids || !centroids_out) return fail("init_centroids / centroids_out is null");
+    if (max_iter < 0) return fail("max_iter=%d < 0", max_iter);
+    cudaStream_t s = (cudaStream_t)stream;
+    CU_TRY(cudaSetDevice(h->device));
+    bool use_tc = false;
+    if (pick_path(h, X, d, k, &use_tc)) return 1;
+    if (ensure_ws(h, n_local, d, k, true)) return 1;
+    const size_t kd = (size_t)k * d;
+    const int64_t acc_len = (int64_t)kd + k + 1;
+
+    CU_TRY(cudaMemcpyAsync(h->d_C, init_centroids, sizeof(float) * kd, cudaMemcpyDeviceToDevice, s));
+    if (!use_tc) launch_rownorm(X, n_local, d, h->d_xnorm, s);
+    launch_prep(h->d_C, k, d, h->d_cnorm, h->d_acc, acc_len, h->d_state, true, s);
+    h->launches += use_tc ? 1 : 2;
+    CU_TRY(cudaGetLastError());
+
+    for (int it = 0; it < max_iter; ++it) {
+        const int slot = it % kRing;
+        if (it >= kRing) {
+            CU_TRY(cudaEventSynchronize(h->ev[slot]));
+            if (h->h_state[slot].done) break;
+        }
+        if (run_pass(h, use_tc, X, n_local, d, k, h->d_C, h->d_labels, h->d_best, h->d_acc, true, s)) return 1;
+        if (h->nranks > 1)
+            NCCL_TRY(g_nccl.AllReduce(h->d_acc, h->d_acc, (size_t)acc_len, ncclFloat64, ncclSum, h->comm, s));
+        launch_finalize(h->d_C, k, d, h->d_cnorm, h->d_acc, h->d_shift, tol, h->d_state, s);
+        h->launches += 1;
+        CU_TRY(cudaGetLastError());
+        CU_TRY(cudaMemcpyAsync(&h->h_state[slot], h->d_state, sizeof(IterState), cudaMemcpyDeviceToHost, s));
+        CU_TRY(cudaEventRecord(h->ev[slot], s));
+    }
+
+    double* d_inertia = h->d_acc + kd + k;
+    if (inertia_out || labels_out) {
+        int32_t* lab = labels_out ? labels_out : h->d_labels;
+        if (run_pass(h, use_tc, X, n_local, d, k, h->d_C, lab, h->d_best, nullptr, false, s)) return 1;
+        CU_TRY(cudaMemsetAsync(d_inertia, 0, sizeof(double), s));
+        launch_sum_best(h->d_best, n_local, d_inertia, s);
+        h->launches += 1;
+        CU_TRY(cudaGetLastError());
+        if (h->nranks > 1)
+            NCCL_TRY(g_nccl.AllReduce(d_inertia, d_inertia, 1, ncclFloat64, ncclSum, h->comm, s));
+        CU_TRY(cudaMemcpyAsync(h->h_scalar, d_inertia, sizeof(double), cudaMemcpyDeviceToHost, s));
+    }
+    CU_TRY(cudaMemcpyAsync(centroids_out, h->d_C, sizeof(float) * kd, cudaMemcpyDeviceToDevice, s));
+    CU_TRY(cudaMemcpyAsync(&h->h_state[kRing], h->d_state, sizeof(IterState), cudaMemcpyDeviceToHost, s));
+    CU_TRY(cudaStreamSynchronize(s));
+    if (n_iter_out) *n_iter_out = h->h_state[kRing].n_iter;
+    if (inertia_out) *inertia_out = h->h_scalar[0];
+    return 0;
+}
+
+int b200km_lloyd_step(b200km_handle* h, const float* X, int64_t n, int d, int k, const float* centroids,
+                      double* sums_out, double* counts_out, double* inertia_out, int32_t* labels_out,
+                      void* stream) {
+    if (check_shape(h, X, n, d, k)) return 1;
+    if (!centroids || !sums_out || !counts_out || !inertia_out) return fail("null output / centroids");
+    cudaStream_t s = (cudaStream_t)stream;
+    CU_TRY(cudaSetDevice(h->device));
+    bool use_tc = false;
+    if (pick_path(h, X, d, k, &use_tc)) return 1;
+    if (ensure_ws(h, n, d, k, true)) return 1;
+    const size_t kd = (size_t)k * d;
+    if (!use_tc) launch_rownorm(X, n, d, h->d_xnorm, s);
+    launch_prep(centroids, k, d, h->d_cnorm, h->d_acc, (int64_t)kd + k + 1, h->d_state, true, s);
+    CU_TRY(cudaGetLastError());
+    int32_t* lab = labels_out ? labels_out : h->d_labels;
+    if (n > 0 && run_pass(h, use_tc, X, n, d, k, centroids, lab, h->d_best, h->d_acc, false, s)) return 1;
+    CU_TRY(cudaMemcpyAsync(sums_out, h->d_acc, sizeof(double) * kd, cudaMemcpyDeviceToDevice, s));
+    CU_TRY(cudaMemcpyAsync(counts_out, h->d_acc + kd, sizeof(double) * k, cudaMemcpyDeviceToDevice, s));
+    CU_TRY(cudaMemcpyAsync(inertia_out, h->d_acc + kd + k, sizeof(double), cudaMemcpyDeviceToDevice, s));
+    return 0;
+}
+
+int b200km_predict(b200km_handle* h, const float* X, int64_t n, int d, const float* centroids, int k,
+                   int32_t* labels_out, float* min_dist_out, void* stream) {
+    if (check_shape(h, X, n, d, k)) return 1;
+    if (!centroids) return fail("centroids is null");
+    if (n == 0) return 0;
+    if (!labels_out) return fail("labels_out is null");
+    cudaStream_t s = (cudaStream_t)stream;
+    CU_TRY(cudaSetDevice(h->device));
+    bool use_tc = false;
+    if (pick_path(h, X, d, k, &use_tc)) return 1;
+    if (ensure_ws(h, n, d, k, true)) return 1;
+    if (!use_tc) launch_rownorm(X, n, d, h->d_xnorm, s);
+    launch_prep(centroids, k, d, h->d_cnorm, nullptr, 0, h->d_state, false, s);
+    CU_TRY(cudaGetLastError());
+    float* best = min_dist_out ? min_dist_out : h->d_best;
+    return run_pass(h, use_tc, X, n, d, k, centroids, labels_out, best, nullptr, false, s);
+}
+
+int b200km_init_centroids(b200km_handle* h, const float* X, int64_t n_local, int d, int k, int mode,
+                          uint64_t seed, double oversampling, float* centroids_out, void* stream) {
+    if (check_shape(h, X, n_local, d, k)) return 1;
+    if (!centroids_out) return fail("centroids_out is null");
+    (void)oversampling;
+    cudaStream_t s = (cudaStream_t)stream;
+    CU_TRY(cudaSetDevice(h->device));
+    if (mode != B200KM_INIT_RANDOM)
+        return fail("init mode %d is not implemented in the C ABI (k-means|| runs in the Python host layer)", mode);
+    // every rank learns all shard sizes, draws the same k distinct global rows, and contributes the
+    // rows it owns; a float sum all-reduce of the otherwise-zero [k,d] buffer assembles the result.
+    std::vector<long long> sizes(h->nranks, 0);
+    sizes[h->rank] = n_local;
+    if (h->nranks > 1) {
+        if (ensure_ws(h, 0, d, k, false)) return 1;
+        long long* d_sizes = reinterpret_cast<long long*>(h->d_acc);
+        CU_TRY(cudaMemcpyAsync(d_sizes + h->rank, &sizes[h->rank], sizeof(long long), cudaMemcpyHostToDevice, s));
+        NCCL_TRY(g_nccl.AllGather(d_sizes + h->rank, d_sizes, 1, ncclInt64, h->comm, s));
+        CU_TRY(cudaMemcpyAsync(sizes.data(), d_sizes, sizeof(long long) * h->nranks, cudaMemcpyDeviceToHost, s));
+        CU_TRY(cudaStreamSynchronize(s));
+    }
+    long long total = 0, my_off = 0;
+    for (int r = 0; r < h->nranks; ++r) {
+        if (r == h->rank) my_off = total;
+        total += sizes[r];
+    }
+    if (total < k) return fail("k=%d exceeds the number of rows %lld", k, total);
+    std::mt19937_64 rng(seed);
+    std::unordered_set<long long> seen;
+    std::vector<long long> pick;
+    pick.reserve(k);
+    for (long long j = total - k; j < total; ++j) {  // Floyd's distinct sampling
+        std::uniform_int_distribution<long long> dist(0, j);
+        long long t = dist(rng);
+        if (!seen.insert(t).second) {
+            seen.insert(j);
+            t = j;
+        }
+        pick.push_back(t);
+    }
+    std::sort(pick.begin(), pick.end());
+    CU_TRY(cudaMemsetAsync(centroids_out, 0, sizeof(float) * (size_t)k * d, s));
+    for (int j = 0; j < k; ++j) {
+        const long long g = pick[j];
+        if (g >= my_off && g < my_off + n_local)
+            CU_TRY(cudaMemcpyAsync(centroids_out + (size_t)j * d, X + (size_t)(g - my_off) * d, sizeof(float) * d,
+                                   cudaMemcpyDeviceToDevice, s));
+    }
+    if (h->nranks > 1)
+        NCCL_TRY(g_nccl.AllReduce(centroids_out, centroids_out, (size_t)k * d, ncclFloat32, ncclSum, h->comm, s));
+    return 0;
+}
+
+}  // extern "C"

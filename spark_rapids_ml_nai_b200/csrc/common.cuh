@@ -1,0 +1,42 @@
+// Shared declarations for the b200km kernels and the C-ABI layer.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace b200km {
+
+// ---- device-resident iteration state (one per handle) -----------------------------------------
+struct IterState {
+    int done;            // set by finalize when shift^2 < tol
+    int n_iter;          // executed Lloyd iterations
+    unsigned int ticket; // last-block election counter (reset by the elected block)
+    unsigned int amb_count;  // entries in the near-tie work list of the current pass
+    double shift2;       // sum_j ||c_new_j - c_old_j||^2 of the last executed iteration
+    float cnorm_max;     // max_j ||c_j||^2 of the current centroids
+    int pad;
+};
+
+// Near-tie band: a row whose best and second-best approximate scores differ by less than
+// kTieTol * (||x||^2 + max_j ||c_j||^2) is re-decided in float64.  The bound covers the
+// worst-case rounding of both arithmetic paths (FP32 FFMA chains; 3xTF32 with truncated splits).
+constexpr float kTieTol = 4e-6f;
+
+constexpr int kNumSMs = 148;
+
+// ---- generic (SIMT) path, kernels_generic.cu ---------------------------------------------------
+void launch_prep(const float* C, int k, int d, float* cnorm, double* acc, int64_t acc_len,
+                 IterState* st, bool reset_iter, cudaStream_t s);
+void launch_rownorm(const float* X, int64_t n, int d, float* xnorm, cudaStream_t s);
+void launch_assign_ffma(const float* X, int64_t n, int d, const float* C, int k, const float* cnorm,
+                        const float* xnorm, int32_t* labels, float* best, IterState* st,
+                        unsigned int* worklist, bool honor_done, cudaStream_t s);
+void launch_refine(const float* X, int64_t n, int d, const float* C, int k, int32_t* labels,
+                   float* best, IterState* st, const unsigned int* worklist, bool honor_done,
+                   cudaStream_t s);
+void launch_update(const float* X, int64_t n, int d, int k, const int32_t* labels, const float* best,
+                   double* acc, IterState* st, bool honor_done, cudaStream_t s);
+void launch_sum_best(const float* best, int64_t n, double* out, cudaStream_t s);
+void launch_finalize(float* C, int k, int d, float* cnorm, double* acc, double* shift_part,
+                     double tol, IterState* st, cudaStream_t s);
+
+}  // namespace b200km
