@@ -75,6 +75,11 @@ int b200km_set_path(b200km_handle* h, int path);
 /* Name of the path the last compute call on this handle used ("ffma" / "tc"). */
 const char* b200km_last_path(b200km_handle* h);
 
+/* 1 when the fused tcgen05 kernel can run this (d, k): with_update != 0 asks for the fit pass
+ * (assignment + float64 accumulation), 0 for the assignment-only pass.  Diagnostics; no counterpart
+ * in the reference. */
+int b200km_tc_supported(int d, int k, int with_update);
+
 /* Instrumentation for the benchmark.  While enabled, every pass brackets its dominant kernel
  * (the fused tcgen05 kernel, or the FFMA assignment kernel) with a CUDA event pair on the caller's
  * stream and the handle counts its kernel launches.  b200km_profile_read waits for the recorded

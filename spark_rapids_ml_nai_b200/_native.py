@@ -27,6 +27,7 @@ _SIGNATURES = {
     "b200km_abort": (_c.c_int, [_c.c_void_p]),
     "b200km_set_path": (_c.c_int, [_c.c_void_p, _c.c_int]),
     "b200km_last_path": (_c.c_char_p, [_c.c_void_p]),
+    "b200km_tc_supported": (_c.c_int, [_c.c_int, _c.c_int, _c.c_int]),
     "b200km_profile_enable": (_c.c_int, [_c.c_void_p, _c.c_int]),
     "b200km_profile_read": (_c.c_int, [_c.c_void_p, _c.POINTER(_c.c_double), _c.POINTER(_c.c_int),
                                        _c.POINTER(_c.c_longlong)]),
@@ -227,6 +228,10 @@ class Handle:
         _check(load().b200km_init_centroids(self._h, X.data_ptr(), n, d, k, mode, seed, float(oversampling),
                                             out.data_ptr(), _stream_ptr(stream)))
         return out
+
+
+def tc_supported(d: int, k: int, with_update: bool = True) -> bool:
+    return bool(load().b200km_tc_supported(d, k, 1 if with_update else 0))
 
 
 def query_workspace(n: int, d: int, k: int) -> int:

@@ -192,11 +192,12 @@ int check_shape(const b200km_handle* h, const void* X, int64_t n, int d, int k) 
 }
 
 // Picks the kernel path for this shape, honouring a forced path (and failing if it cannot run).
-int pick_path(b200km_handle* h, const float* X, int d, int k, bool* use_tc) {
-    const bool can = tc_supported(X, d, k);
+int pick_path(b200km_handle* h, const float* X, int d, int k, bool with_acc, bool* use_tc) {
+    const bool can = tc_supported(X, d, k, with_acc);
     if (h->path == B200KM_PATH_TC && !can)
         return fail("tcgen05 path forced but not available for d=%d k=%d (needs d%%4==0, 16B-aligned X, "
-                    "d<=%d, k<=%d)", d, k, tc_max_d(), tc_max_k());
+                    "d<=%d, k<=%d and the split centroids%s to fit shared memory)", d, k, tc_max_d(), tc_max_k(),
+                    with_acc ? " + float64 accumulators" : "");
     *use_tc = (h->path == B200KM_PATH_TC) || (h->path == B200KM_PATH_AUTO && can);
     h->last_path = *use_tc ? "tc" : "ffma";
     return 0;
@@ -327,6 +328,10 @@ int b200km_set_path(b200km_handle* h, int path) {
 
 const char* b200km_last_path(b200km_handle* h) { return h ? h->last_path : "none"; }
 
+int b200km_tc_supported(int d, int k, int with_update) {
+    return tc_supported(nullptr, d, k, with_update != 0) ? 1 : 0;
+}
+
 int b200km_profile_enable(b200km_handle* h, int on) {
     if (!h) return fail("null handle");
     CU_TRY(cudaSetDevice(h->device));
@@ -378,7 +383,7 @@ int b200km_fit(b200km_handle* h, const float* X, int64_t n_local, int d, int k, 
     cudaStream_t s = (cudaStream_t)stream;
     CU_TRY(cudaSetDevice(h->device));
     bool use_tc = false;
-    if (pick_path(h, X, d, k, &use_tc)) return 1;
+    if (pick_path(h, X, d, k, true, &use_tc)) return 1;
     if (ensure_ws(h, n_local, d, k, true)) return 1;
     const size_t kd = (size_t)k * d;
     const int64_t acc_len = (int64_t)kd + k + 1;
@@ -433,7 +438,7 @@ int b200km_lloyd_step(b200km_handle* h, const float* X, int64_t n, int d, int k,
     cudaStream_t s = (cudaStream_t)stream;
     CU_TRY(cudaSetDevice(h->device));
     bool use_tc = false;
-    if (pick_path(h, X, d, k, &use_tc)) return 1;
+    if (pick_path(h, X, d, k, true, &use_tc)) return 1;
     if (ensure_ws(h, n, d, k, true)) return 1;
     const size_t kd = (size_t)k * d;
     if (!use_tc) launch_rownorm(X, n, d, h->d_xnorm, s);
@@ -456,7 +461,7 @@ int b200km_predict(b200km_handle* h, const float* X, int64_t n, int d, const flo
     cudaStream_t s = (cudaStream_t)stream;
     CU_TRY(cudaSetDevice(h->device));
     bool use_tc = false;
-    if (pick_path(h, X, d, k, &use_tc)) return 1;
+    if (pick_path(h, X, d, k, false, &use_tc)) return 1;
     if (ensure_ws(h, n, d, k, true)) return 1;
     if (!use_tc) launch_rownorm(X, n, d, h->d_xnorm, s);
     launch_prep(centroids, k, d, h->d_cnorm, nullptr, 0, h->d_state, false, s);

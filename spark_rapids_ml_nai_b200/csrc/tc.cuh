@@ -10,7 +10,7 @@ struct TcWorkspace {
     void* tmap_cache = nullptr;  // host-side cache of encoded tensor maps
 };
 
-bool tc_supported(const float* X, int d, int k);
+bool tc_supported(const float* X, int d, int k, bool with_acc);
 int tc_max_d();
 int tc_max_k();
 size_t tc_workspace_bytes(int d, int k);
