@@ -183,7 +183,11 @@ __global__ void __launch_bounds__(kThreads, 1)
     if (p.honor_done && p.st->done) return;
 
     extern __shared__ uint8_t smem_raw[];
-    uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+    __shared__ int s_hist[4][kMaxK + 8];  // per-epilogue-warp label histograms, then offsets
+    __shared__ int s_base[kMaxK + 8];     // start of every label's run in the sorted order
+    __shared__ int s_perm[kTileM];        // sorted position -> row of the tile
+    // pointer arithmetic (not an integer round trip) keeps the shared address space visible to the compiler
+    uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
     const uint32_t smem_base = smem_u32(smem);
 
     const int warp = threadIdx.x >> 5;
@@ -339,14 +343,12 @@ __global__ void __launch_bounds__(kThreads, 1)
         const int et = threadIdx.x - 6 * 32;  // 0..127 within the epilogue group
         float* cn_s = (float*)(smem + p.off_cn);
         float* xn_s = (float*)(smem + p.off_xn);
-        int* s_lab = (int*)(smem + p.off_sort);
-        int* s_sorted = s_lab + kTileM;
-        int* s_perm = s_sorted + kTileM;
         double* sacc = (double*)(smem + p.off_acc);
         const int acc_n = p.k * p.d + p.k;
         for (int j = et; j < p.k_pad; j += 128) cn_s[j] = (j < p.k) ? p.cnorm[j] : FLT_MAX;
         if (p.acc)
             for (int i = et; i < acc_n; i += 128) sacc[i] = 0.0;
+        for (int i = et; i < 4 * (kMaxK + 8); i += 128) (&s_hist[0][0])[i] = 0;
         const float cmax = p.st->cnorm_max;
         named_bar_sync(1, 128);
 
@@ -433,53 +435,73 @@ __global__ void __launch_bounds__(kThreads, 1)
             }
 
             if (p.acc) {
-                const int rows = (int)((p.n - tile * kTileM) < kTileM ? (p.n - tile * kTileM) : kTileM);
-                const int my = valid ? label : INT_MAX;
-                s_lab[row] = my;
+                // ---- stable counting sort of the tile's rows by label (bin k = rows past the end) ----
+                const int bins = p.k + 1;
+                const int bin = valid ? label : p.k;
+                const unsigned peers = __match_any_sync(0xffffffffu, bin);
+                const int rank_w = __popc(peers & ((1u << lane) - 1u));
+                if (rank_w == 0) s_hist[q][bin] = __popc(peers);
                 named_bar_sync(1, 128);
-                int rank = 0;
-#pragma unroll 8
-                for (int t = 0; t < kTileM; ++t) {
-                    const int o = s_lab[t];
-                    rank += (o < my) || (o == my && t < row);
-                }
-                s_sorted[rank] = my;
-                s_perm[rank] = row;
-                if (valid) atomicAdd(&sacc[p.k * p.d + my], 1.0);
-                named_bar_sync(1, 128);
-                // warp q owns sorted positions [32q, 32q+32); lane L owns float4 column chunk L (+32, ...)
-                const int p0 = q * 32;
-                const int p1 = (p0 + 32 < rows) ? p0 + 32 : rows;
-                const int nchunks = p.d >> 2;
-                for (int ch = lane; ch < nchunks; ch += 32) {
-                    if (p0 >= p1) break;
-                    const int a = ch >> 3, c = ch & 7;
-                    int cur = s_sorted[p0];
-                    float4 run = make_float4(0.f, 0.f, 0.f, 0.f);
-                    for (int pp = p0; pp < p1; ++pp) {
-                        const int r = s_perm[pp];
-                        const int l = s_sorted[pp];
-                        const float4 v = *reinterpret_cast<const float4*>(stage + a * kAtomBytes + r * 128 +
-                                                                          ((c ^ (r & 7)) << 4));
-                        if (l != cur) {
-                            double* dst = sacc + (size_t)cur * p.d + ch * 4;
-                            atomicAdd(dst + 0, (double)run.x);
-                            atomicAdd(dst + 1, (double)run.y);
-                            atomicAdd(dst + 2, (double)run.z);
-                            atomicAdd(dst + 3, (double)run.w);
-                            run = make_float4(0.f, 0.f, 0.f, 0.f);
-                            cur = l;
-                        }
-                        run.x += v.x;
-                        run.y += v.y;
-                        run.z += v.z;
-                        run.w += v.w;
+                if (q == 0) {
+                    // one warp turns the 4 per-warp histograms into offsets; lane owns `per` consecutive bins
+                    const int per = (bins + 31) >> 5;
+                    const int b0 = lane * per;
+                    int lane_total = 0;
+                    for (int b = b0; b < b0 + per && b < bins; ++b)
+                        lane_total += s_hist[0][b] + s_hist[1][b] + s_hist[2][b] + s_hist[3][b];
+                    int incl = lane_total;
+#pragma unroll
+                    for (int o = 1; o < 32; o <<= 1) {
+                        const int v = __shfl_up_sync(0xffffffffu, incl, o);
+                        if (lane >= o) incl += v;
                     }
-                    double* dst = sacc + (size_t)cur * p.d + ch * 4;
-                    atomicAdd(dst + 0, (double)run.x);
-                    atomicAdd(dst + 1, (double)run.y);
-                    atomicAdd(dst + 2, (double)run.z);
-                    atomicAdd(dst + 3, (double)run.w);
+                    int run = incl - lane_total;
+                    for (int b = b0; b < b0 + per && b < bins; ++b) {
+                        const int h0 = s_hist[0][b], h1 = s_hist[1][b], h2 = s_hist[2][b], h3 = s_hist[3][b];
+                        s_base[b] = run;
+                        s_hist[0][b] = run;
+                        s_hist[1][b] = run + h0;
+                        s_hist[2][b] = run + h0 + h1;
+                        s_hist[3][b] = run + h0 + h1 + h2;
+                        const int tot = h0 + h1 + h2 + h3;
+                        if (b < p.k && tot) sacc[p.k * p.d + b] += (double)tot;  // sole owner of this count
+                        run += tot;
+                    }
+                    if (lane == 31) s_base[bins] = run;
+                }
+                named_bar_sync(1, 128);
+                s_perm[s_hist[q][bin] + rank_w] = row;
+                __syncwarp();
+                for (int b = lane; b < bins; b += 32) s_hist[q][b] = 0;  // own row only: ready for the next tile
+                named_bar_sync(1, 128);
+                // ---- label-owned accumulation: warp q adds the rows of labels q, q+4, ...; lane = float4
+                // column chunk.  Every (label, column) has one owner per tile: plain float64 RMW, no atomics.
+                const int nchunks = p.d >> 2;
+                for (int l = q; l < p.k; l += 4) {
+                    const int beg = s_base[l], end = s_base[l + 1];
+                    if (beg == end) continue;
+                    for (int ch = lane; ch < nchunks; ch += 32) {
+                        const uint8_t* colp = stage + (ch >> 3) * kAtomBytes;
+                        const int c = ch & 7;
+                        float4 run = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll 4
+                        for (int pp = beg; pp < end; ++pp) {
+                            const int r = s_perm[pp];
+                            const float4 v = *reinterpret_cast<const float4*>(colp + r * 128 + ((c ^ (r & 7)) << 4));
+                            run.x += v.x;
+                            run.y += v.y;
+                            run.z += v.z;
+                            run.w += v.w;
+                        }
+                        double2* dst = reinterpret_cast<double2*>(sacc + (size_t)l * p.d + ch * 4);
+                        double2 a0 = dst[0], a1 = dst[1];
+                        a0.x += (double)run.x;
+                        a0.y += (double)run.y;
+                        a1.x += (double)run.z;
+                        a1.y += (double)run.w;
+                        dst[0] = a0;
+                        dst[1] = a1;
+                    }
                 }
             }
             __syncwarp();
@@ -567,6 +589,7 @@ Plan make_plan(int d, int k, bool with_acc) {
     fixed += 3 * kTileM * 4;           // sort arrays
     fixed += 512;                      // barriers + tmem slot
     fixed += 1024;                     // alignment slack
+    fixed += 6 * 1024;                 // static shared arrays of the kernel (histograms, offsets, permutation)
     int S = (kMaxSmem - fixed) / stage;
     if (S > kMaxStages) S = kMaxStages;
     if (S < 2) return pl;
@@ -586,7 +609,7 @@ Plan make_plan(int d, int k, bool with_acc) {
     pl.off_bar = off;
     off += 512;
     pl.total = off + 1024;
-    pl.ok = pl.total <= kMaxSmem;
+    pl.ok = pl.total + 6 * 1024 <= kMaxSmem;
     return pl;
 }
 
@@ -635,9 +658,15 @@ int tc_pass(TcWorkspace* ws, const float* X, int64_t n, int d, int k, const floa
 
     static bool attr_set = false;
     if (!attr_set) {
-        if (cudaFuncSetAttribute(kmeans_fused_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxSmem) !=
+        cudaFuncAttributes fa;
+        if (cudaFuncGetAttributes(&fa, kmeans_fused_tc_kernel) != cudaSuccess || fa.sharedSizeBytes > 6 * 1024) {
+            snprintf(g_tc_err, sizeof(g_tc_err), "unexpected static shared memory size of the fused kernel");
+            return 1;
+        }
+        const int max_dyn = kMaxSmem - (int)fa.sharedSizeBytes;
+        if (cudaFuncSetAttribute(kmeans_fused_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, max_dyn) !=
             cudaSuccess) {
-            snprintf(g_tc_err, sizeof(g_tc_err), "cannot raise dynamic shared memory to %d bytes", kMaxSmem);
+            snprintf(g_tc_err, sizeof(g_tc_err), "cannot raise dynamic shared memory to %d bytes", max_dyn);
             return 1;
         }
         attr_set = true;
