@@ -24,6 +24,7 @@
 #include <cfloat>
 #include <climits>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 
 namespace b200km {
@@ -55,6 +56,7 @@ struct TcParams {
     IterState* st;
     int honor_done;
     float tie_tol;
+    unsigned long long* trace;  // development aid (B200KM_TRACE): [256 tiles][8 events] clock64 of CTA 0
     // shared-memory offsets (bytes from the 1024-aligned base)
     int off_c, off_acc, off_cn, off_xn, off_sort, off_bar;
 };
@@ -71,18 +73,24 @@ __device__ __forceinline__ void mbar_arrive(uint32_t bar) {
 __device__ __forceinline__ void mbar_arrive_expect_tx(uint32_t bar, uint32_t bytes) {
     asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
 }
-__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+__device__ __forceinline__ bool mbar_try(uint32_t bar, uint32_t parity) {
+    uint32_t ok;
     asm volatile(
         "{\n\t"
         ".reg .pred p;\n\t"
-        "WAIT_LOOP:\n\t"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
-        "@p bra DONE;\n\t"
-        "bra WAIT_LOOP;\n\t"
-        "DONE:\n\t"
-        "}" ::"r"(bar),
-        "r"(parity)
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t"
+        "}"
+        : "=r"(ok)
+        : "r"(bar), "r"(parity)
         : "memory");
+    return ok != 0;
+}
+// Polls with a short sleep between probes: a warp that spins on try_wait competes for issue slots with
+// the warps doing the work on its scheduler (measured: the spinning roles slowed the others ~2x).
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+    if (mbar_try(bar, parity)) return;
+    while (!mbar_try(bar, parity)) __nanosleep(40);
 }
 __device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* tm, uint32_t bar, int c0, int c1) {
     asm volatile(
@@ -151,6 +159,18 @@ __device__ __forceinline__ uint32_t tile_off(int r, int i) {
     return (uint32_t)(a * kAtomBytes + r * 128 + (((c ^ (r & 7)) << 4) | (e << 2)));
 }
 
+__device__ __forceinline__ bool elect_one() {
+    uint32_t pred;
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p;\n\t"
+        "elect.sync _|p, 0xffffffff;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t"
+        "}"
+        : "=r"(pred));
+    return pred != 0;
+}
+
 __device__ __forceinline__ uint32_t tf32_trunc(uint32_t bits) { return bits & 0xFFFFE000u; }
 __device__ __forceinline__ uint32_t tf32_round(uint32_t bits) { return (bits + 0x1000u) & 0xFFFFE000u; }
 
@@ -158,6 +178,10 @@ struct Best {
     float b1, b2;
     int i1;
 };
+
+__device__ __forceinline__ void trace_ev(const TcParams& p, int64_t it, int ev) {
+    if (p.trace && blockIdx.x == 0 && it < 256) p.trace[it * 8 + ev] = (unsigned long long)clock64();
+}
 
 // ------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256) split_centroids_kernel(const float* __restrict__ C, int k, int d, int k_pad,
@@ -243,15 +267,16 @@ __global__ void __launch_bounds__(kThreads, 1)
         // ===================================== TMA producer =====================================
         if (lane == 0) {
             mbar_arrive_expect_tx(c_full, (uint32_t)(2 * p.n_atoms * c_block));
-            for (int part = 0; part < 2; ++part)
-                for (int a = 0; a < p.n_atoms; ++a)
-                    tma_load_2d(smem_base + p.off_c + (part * p.n_atoms + a) * c_block, &tmC, c_full, a * 32,
+            for (int a = 0; a < p.n_atoms; ++a)
+                for (int part = 0; part < 2; ++part)  // atom block = [c_hi rows | c_lo rows], 2*k_pad rows
+                    tma_load_2d(smem_base + p.off_c + (2 * a + part) * c_block, &tmC, c_full, a * 32,
                                 part * p.k_pad);
             int64_t it = 0;
             for (int64_t tile = first_tile; tile < p.num_tiles; tile += tile_step, ++it) {
                 const int s = (int)(it % S);
                 const uint32_t ph = (uint32_t)((it / S) & 1);
                 mbar_wait(x_empty(s), ph ^ 1u);
+                trace_ev(p, it, 0);
                 mbar_arrive_expect_tx(x_full(s), (uint32_t)stage_bytes);
                 for (int a = 0; a < p.n_atoms; ++a)
                     tma_load_2d(smem_base + s * stage_bytes + a * kAtomBytes, &tmX, x_full(s), a * 32,
@@ -261,8 +286,16 @@ __global__ void __launch_bounds__(kThreads, 1)
         __syncwarp();
     } else if (warp == 1) {
         // ====================================== MMA issuer ======================================
-        const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(p.k_pad >> 3) << 17) |
-                               ((uint32_t)(kTileM >> 4) << 24);
+        // The whole warp runs the loop and one elected lane issues (a tcgen05.mma issued from divergent
+        // code costs ~100 cycles per instruction, ~40 from warp-uniform code: tools/mma_bench.cu).
+        // k_pad <= 128: B is the stacked block [c_hi ; c_lo] (N = 2*k_pad), so a K-step is two instructions of
+        // one shape:  D[:, 0:2k) (+)= x_hi.[c_hi;c_lo]^T   and   D[:, 0:2k) += x_lo.[c_hi;c_lo]^T  (all four
+        // partial products of (x_hi+x_lo).(c_hi+c_lo)).
+        const uint32_t idesc_base = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(kTileM >> 4) << 24);
+        const uint32_t idesc_n = idesc_base | ((uint32_t)(p.k_pad >> 3) << 17);
+        const uint32_t idesc_2n = idesc_base | ((uint32_t)((2 * p.k_pad) >> 3) << 17);
+        const bool stacked = p.k_pad <= 128;
+        const int dcols = stacked ? 2 * p.k_pad : p.k_pad;
         mbar_wait(c_full, 0);
         int64_t it = 0;   // tile counter
         int64_t ait = 0;  // atom counter (ring position)
@@ -270,27 +303,35 @@ __global__ void __launch_bounds__(kThreads, 1)
             const int db = (int)(it % ND);
             mbar_wait(d_empty(db), (uint32_t)(((it / ND) & 1) ^ 1));
             tc_fence_after();
-            const uint32_t d_tmem = tmem_base + (uint32_t)(db * p.k_pad);
+            const uint32_t d_tmem = tmem_base + (uint32_t)(db * dcols);
             for (int a = 0; a < p.n_atoms; ++a, ++ait) {
                 const int slot = (int)(ait % kRing);
                 mbar_wait(a_full(slot), (uint32_t)((ait / kRing) & 1));
                 tc_fence_after();
-                if (lane == 0) {
-                    const int rem = p.d - a * 32;
-                    const int ksteps = rem >= 32 ? 4 : (rem + 7) >> 3;
-                    const uint32_t a_hi = tmem_base + (uint32_t)(kRingCol0 + slot * 64);
-                    const uint32_t a_lo = a_hi + 32;
-                    const uint32_t b_hi = smem_base + p.off_c + a * c_block;
-                    const uint32_t b_lo = smem_base + p.off_c + (p.n_atoms + a) * c_block;
-                    for (int kk = 0; kk < ksteps; ++kk) {
-                        const uint64_t dh = make_b_desc(b_hi + kk * 32);
+                const int rem = p.d - a * 32;
+                const int ksteps = rem >= 32 ? 4 : (rem + 7) >> 3;
+                const uint32_t a_hi = tmem_base + (uint32_t)(kRingCol0 + slot * 64);
+                const uint32_t a_lo = a_hi + 32;
+                const uint32_t b_hi = smem_base + p.off_c + (2 * a) * c_block;
+                const uint32_t b_lo = b_hi + c_block;
+                for (int kk = 0; kk < ksteps; ++kk) {
+                    const uint64_t dh = make_b_desc(b_hi + kk * 32);
+                    if (stacked) {
+                        // same shape and same B for both: D[:,0:k) += (x_hi+x_lo).c_hi, D[:,k:2k) += (x_hi+x_lo).c_lo
+                        // (alternating instruction shapes between consecutive MMAs stalls the tensor pipe)
+                        if (elect_one()) mma_tf32_ts(d_tmem, a_hi + 8 * kk, dh, idesc_2n, (a | kk) != 0);
+                        if (elect_one()) mma_tf32_ts(d_tmem, a_lo + 8 * kk, dh, idesc_2n, 1);
+                    } else {
                         const uint64_t dl = make_b_desc(b_lo + kk * 32);
-                        mma_tf32_ts(d_tmem, a_lo + 8 * kk, dh, idesc, (a | kk) != 0);
-                        mma_tf32_ts(d_tmem, a_hi + 8 * kk, dl, idesc, 1);
-                        mma_tf32_ts(d_tmem, a_hi + 8 * kk, dh, idesc, 1);
+                        if (elect_one()) mma_tf32_ts(d_tmem, a_lo + 8 * kk, dh, idesc_n, (a | kk) != 0);
+                        if (elect_one()) mma_tf32_ts(d_tmem, a_hi + 8 * kk, dl, idesc_n, 1);
+                        if (elect_one()) mma_tf32_ts(d_tmem, a_hi + 8 * kk, dh, idesc_n, 1);
                     }
-                    tc_commit(a_empty(slot));
-                    if (a == p.n_atoms - 1) tc_commit(d_full(db));
+                }
+                if (elect_one()) tc_commit(a_empty(slot));
+                if (a == p.n_atoms - 1) {
+                    if (elect_one()) tc_commit(d_full(db));
+                    if (lane == 0) trace_ev(p, it, 3);
                 }
                 __syncwarp();
             }
@@ -304,6 +345,7 @@ __global__ void __launch_bounds__(kThreads, 1)
         for (int64_t tile = first_tile; tile < p.num_tiles; tile += tile_step, ++it) {
             const int s = (int)(it % S);
             mbar_wait(x_full(s), (uint32_t)((it / S) & 1));
+            if (threadIdx.x == 64) trace_ev(p, it, 1);
             const uint8_t* stage = smem + (size_t)s * stage_bytes;
             float xn = 0.f;
             for (int a = 0; a < p.n_atoms; ++a, ++ait) {
@@ -335,6 +377,7 @@ __global__ void __launch_bounds__(kThreads, 1)
             xn_s[s * kTileM + row] = xn;
             __syncwarp();
             if (lane == 0) mbar_arrive(xn_full(s));
+            if (threadIdx.x == 64) trace_ev(p, it, 2);
         }
     } else {
         // ======================================= epilogue =======================================
@@ -350,6 +393,8 @@ __global__ void __launch_bounds__(kThreads, 1)
             for (int i = et; i < acc_n; i += 128) sacc[i] = 0.0;
         for (int i = et; i < 4 * (kMaxK + 8); i += 128) (&s_hist[0][0])[i] = 0;
         const float cmax = p.st->cnorm_max;
+        const bool stacked = p.k_pad <= 128;
+        const int dcols = stacked ? 2 * p.k_pad : p.k_pad;
         named_bar_sync(1, 128);
 
         double inert = 0.0;
@@ -363,19 +408,24 @@ __global__ void __launch_bounds__(kThreads, 1)
             tc_fence_after();
             mbar_wait(x_full(s), (uint32_t)((it / S) & 1));
             mbar_wait(xn_full(s), (uint32_t)((it / S) & 1));
+            if (et == 0) trace_ev(p, it, 4);
 
+            // ---- scores -> running (best, second, argmin) ----
             Best b;
             b.b1 = FLT_MAX;
             b.b2 = FLT_MAX;
             b.i1 = 0;
-            const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(db * p.k_pad);
+            const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(db * dcols);
             for (int c0 = 0; c0 < p.k_pad; c0 += 16) {
-                uint32_t r[16];
+                uint32_t r[16], r2[16];
                 tmem_ld16(taddr + c0, r);
+                if (stacked) tmem_ld16(taddr + p.k_pad + c0, r2);
                 tmem_wait_ld();
 #pragma unroll
                 for (int j = 0; j < 16; ++j) {
-                    const float sc = fmaf(-2.f, __uint_as_float(r[j]), cn_s[c0 + j]);
+                    float dot = __uint_as_float(r[j]);
+                    if (stacked) dot += __uint_as_float(r2[j]);
+                    const float sc = fmaf(-2.f, dot, cn_s[c0 + j]);
                     if (sc < b.b1) {
                         b.b2 = b.b1;
                         b.b1 = sc;
@@ -385,42 +435,65 @@ __global__ void __launch_bounds__(kThreads, 1)
                     }
                 }
             }
+            const float xn = xn_s[s * kTileM + row];
+            const float band = p.tie_tol * (xn + cmax);
+            const bool amb = valid && p.k > 1 && (b.b2 - b.b1) < band;
+            unsigned m = __ballot_sync(0xffffffffu, amb);
+            // near-tie rows: second look at the scores to list the candidates inside the band (up to 4)
+            int ncand = 0, cand0 = 0, cand1 = 0, cand2 = 0, cand3 = 0;
+            if (m) {
+                for (int c0 = 0; c0 < p.k_pad; c0 += 16) {
+                    uint32_t r[16], r2[16];
+                    tmem_ld16(taddr + c0, r);
+                    if (stacked) tmem_ld16(taddr + p.k_pad + c0, r2);
+                    tmem_wait_ld();
+#pragma unroll
+                    for (int j = 0; j < 16; ++j) {
+                        float dot = __uint_as_float(r[j]);
+                        if (stacked) dot += __uint_as_float(r2[j]);
+                        const float sc = fmaf(-2.f, dot, cn_s[c0 + j]);
+                        if (amb && (c0 + j) < p.k && (sc - b.b1) < band) {
+                            if (ncand == 0) cand0 = c0 + j;
+                            else if (ncand == 1) cand1 = c0 + j;
+                            else if (ncand == 2) cand2 = c0 + j;
+                            else if (ncand == 3) cand3 = c0 + j;
+                            ++ncand;
+                        }
+                    }
+                }
+            }
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(d_empty(db));
 
-            const float xn = xn_s[s * kTileM + row];
             const uint8_t* stage = smem + (size_t)s * stage_bytes;
             int label = b.i1;
             float bestv = fmaxf(xn + b.b1, 0.f);
-            const bool amb = valid && p.k > 1 && (b.b2 - b.b1) < p.tie_tol * (xn + cmax);
-            unsigned m = __ballot_sync(0xffffffffu, amb);
+            // ---- float64 re-decision, warp-cooperative: lanes split the d dimension ----
             while (m) {
                 const int src = __ffs(m) - 1;
                 m &= m - 1;
                 const int rr = q * 32 + src;
+                const int nc = __shfl_sync(0xffffffffu, ncand, src);
+                const int c_0 = __shfl_sync(0xffffffffu, cand0, src), c_1 = __shfl_sync(0xffffffffu, cand1, src);
+                const int c_2 = __shfl_sync(0xffffffffu, cand2, src), c_3 = __shfl_sync(0xffffffffu, cand3, src);
+                const int total = nc <= 4 ? nc : p.k;  // more than 4 candidates: scan every centroid
                 double bd = DBL_MAX;
-                int bi = INT_MAX;
-                for (int j = lane; j < p.k; j += 32) {
+                int bi = 0;
+                for (int t = 0; t < total; ++t) {
+                    const int j = nc <= 4 ? (t == 0 ? c_0 : t == 1 ? c_1 : t == 2 ? c_2 : c_3) : t;
                     const float* c = p.C + (size_t)j * p.d;
                     double sum = 0.0;
-                    for (int i = 0; i < p.d; ++i) {
+                    for (int i = lane; i < p.d; i += 32) {
                         const float xv = *reinterpret_cast<const float*>(stage + tile_off(rr, i));
                         const double df = (double)xv - (double)__ldg(c + i);
                         sum = fma(df, df, sum);
                     }
-                    if (sum < bd) {
+#pragma unroll
+                    for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+                    if (sum < bd) {  // candidates come in ascending index order: ties keep the lowest
                         bd = sum;
                         bi = j;
-                    }
-                }
-#pragma unroll
-                for (int o = 16; o > 0; o >>= 1) {
-                    const double od = __shfl_xor_sync(0xffffffffu, bd, o);
-                    const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
-                    if (od < bd || (od == bd && oi < bi)) {
-                        bd = od;
-                        bi = oi;
                     }
                 }
                 if (lane == src) {
@@ -434,6 +507,7 @@ __global__ void __launch_bounds__(kThreads, 1)
                 inert += (double)bestv;
             }
 
+            if (et == 0) trace_ev(p, it, 5);
             if (p.acc) {
                 // ---- stable counting sort of the tile's rows by label (bin k = rows past the end) ----
                 const int bins = p.k + 1;
@@ -447,8 +521,8 @@ __global__ void __launch_bounds__(kThreads, 1)
                     const int per = (bins + 31) >> 5;
                     const int b0 = lane * per;
                     int lane_total = 0;
-                    for (int b = b0; b < b0 + per && b < bins; ++b)
-                        lane_total += s_hist[0][b] + s_hist[1][b] + s_hist[2][b] + s_hist[3][b];
+                    for (int bb = b0; bb < b0 + per && bb < bins; ++bb)
+                        lane_total += s_hist[0][bb] + s_hist[1][bb] + s_hist[2][bb] + s_hist[3][bb];
                     int incl = lane_total;
 #pragma unroll
                     for (int o = 1; o < 32; o <<= 1) {
@@ -456,44 +530,77 @@ __global__ void __launch_bounds__(kThreads, 1)
                         if (lane >= o) incl += v;
                     }
                     int run = incl - lane_total;
-                    for (int b = b0; b < b0 + per && b < bins; ++b) {
-                        const int h0 = s_hist[0][b], h1 = s_hist[1][b], h2 = s_hist[2][b], h3 = s_hist[3][b];
-                        s_base[b] = run;
-                        s_hist[0][b] = run;
-                        s_hist[1][b] = run + h0;
-                        s_hist[2][b] = run + h0 + h1;
-                        s_hist[3][b] = run + h0 + h1 + h2;
+                    for (int bb = b0; bb < b0 + per && bb < bins; ++bb) {
+                        const int h0 = s_hist[0][bb], h1 = s_hist[1][bb], h2 = s_hist[2][bb], h3 = s_hist[3][bb];
+                        s_base[bb] = run;
+                        s_hist[0][bb] = run;
+                        s_hist[1][bb] = run + h0;
+                        s_hist[2][bb] = run + h0 + h1;
+                        s_hist[3][bb] = run + h0 + h1 + h2;
                         const int tot = h0 + h1 + h2 + h3;
-                        if (b < p.k && tot) sacc[p.k * p.d + b] += (double)tot;  // sole owner of this count
+                        if (bb < p.k && tot) sacc[p.k * p.d + bb] += (double)tot;  // sole owner of this count
                         run += tot;
                     }
                     if (lane == 31) s_base[bins] = run;
                 }
                 named_bar_sync(1, 128);
-                s_perm[s_hist[q][bin] + rank_w] = row;
+                s_perm[s_hist[q][bin] + rank_w] = row | (bin << 8);  // sorted position -> (row, label)
                 __syncwarp();
-                for (int b = lane; b < bins; b += 32) s_hist[q][b] = 0;  // own row only: ready for the next tile
+                for (int bb = lane; bb < bins; bb += 32) s_hist[q][bb] = 0;  // own row only: ready for the next tile
                 named_bar_sync(1, 128);
-                // ---- label-owned accumulation: warp q adds the rows of labels q, q+4, ...; lane = float4
-                // column chunk.  Every (label, column) has one owner per tile: plain float64 RMW, no atomics.
+                if (et == 0) trace_ev(p, it, 6);
+                // ---- accumulation: warp q owns the labels [q*k/4, (q+1)*k/4), i.e. one contiguous range of
+                // sorted positions; lane = float4 column chunk.  Consecutive equal-label rows are summed in
+                // FP32 registers and flushed once per run with a plain float64 read-modify-write (every
+                // (label, column) has exactly one owner per tile, so no atomics are needed).
+                const int l_lo = (q * p.k) >> 2, l_hi = ((q + 1) * p.k) >> 2;
+                const int pb = s_base[l_lo], pe = s_base[l_hi];
                 const int nchunks = p.d >> 2;
-                for (int l = q; l < p.k; l += 4) {
-                    const int beg = s_base[l], end = s_base[l + 1];
-                    if (beg == end) continue;
-                    for (int ch = lane; ch < nchunks; ch += 32) {
-                        const uint8_t* colp = stage + (ch >> 3) * kAtomBytes;
-                        const int c = ch & 7;
-                        float4 run = make_float4(0.f, 0.f, 0.f, 0.f);
-#pragma unroll 4
-                        for (int pp = beg; pp < end; ++pp) {
-                            const int r = s_perm[pp];
-                            const float4 v = *reinterpret_cast<const float4*>(colp + r * 128 + ((c ^ (r & 7)) << 4));
-                            run.x += v.x;
-                            run.y += v.y;
-                            run.z += v.z;
-                            run.w += v.w;
+                for (int ch = lane; ch < nchunks; ch += 32) {
+                    const uint8_t* colp = stage + (ch >> 3) * kAtomBytes;
+                    const int c = ch & 7;
+                    int cur = -1;
+                    float4 run = make_float4(0.f, 0.f, 0.f, 0.f);
+                    for (int base = pb; base < pe; base += 8) {
+                        float4 v[8];
+                        int pl[8];
+#pragma unroll
+                        for (int j = 0; j < 8; ++j) {
+                            const int pos = base + j < pe ? base + j : pe - 1;
+                            pl[j] = s_perm[pos];
                         }
-                        double2* dst = reinterpret_cast<double2*>(sacc + (size_t)l * p.d + ch * 4);
+#pragma unroll
+                        for (int j = 0; j < 8; ++j) {
+                            const int r = pl[j] & 127;
+                            v[j] = *reinterpret_cast<const float4*>(colp + r * 128 + ((c ^ (r & 7)) << 4));
+                        }
+#pragma unroll
+                        for (int j = 0; j < 8; ++j) {
+                            if (base + j < pe) {
+                                const int l = pl[j] >> 8;
+                                if (l != cur) {
+                                    if (cur >= 0) {
+                                        double2* dst = reinterpret_cast<double2*>(sacc + (size_t)cur * p.d + ch * 4);
+                                        double2 a0 = dst[0], a1 = dst[1];
+                                        a0.x += (double)run.x;
+                                        a0.y += (double)run.y;
+                                        a1.x += (double)run.z;
+                                        a1.y += (double)run.w;
+                                        dst[0] = a0;
+                                        dst[1] = a1;
+                                    }
+                                    run = make_float4(0.f, 0.f, 0.f, 0.f);
+                                    cur = l;
+                                }
+                                run.x += v[j].x;
+                                run.y += v[j].y;
+                                run.z += v[j].z;
+                                run.w += v[j].w;
+                            }
+                        }
+                    }
+                    if (cur >= 0) {
+                        double2* dst = reinterpret_cast<double2*>(sacc + (size_t)cur * p.d + ch * 4);
                         double2 a0 = dst[0], a1 = dst[1];
                         a0.x += (double)run.x;
                         a0.y += (double)run.y;
@@ -506,6 +613,7 @@ __global__ void __launch_bounds__(kThreads, 1)
             }
             __syncwarp();
             if (lane == 0) mbar_arrive(x_empty(s));
+            if (et == 0) trace_ev(p, it, 7);
         }
 
         if (p.acc) {
@@ -578,7 +686,7 @@ Plan make_plan(int d, int k, bool with_acc) {
     pl.k_pad = (k + 15) & ~15;
     pl.n_atoms = (d + 31) / 32;
     pl.d_pad = pl.n_atoms * 32;
-    pl.num_d = pl.k_pad <= 128 ? 2 : 1;
+    pl.num_d = (pl.k_pad <= 128 ? 2 * pl.k_pad : pl.k_pad) <= 128 ? 2 : 1;  // D buffers in TMEM columns [0,256)
     const int stage = pl.n_atoms * kAtomBytes;
     const int c_bytes = 2 * pl.n_atoms * pl.k_pad * 128;
     int fixed = c_bytes;
@@ -704,6 +812,12 @@ int tc_pass(TcWorkspace* ws, const float* X, int64_t n, int d, int k, const floa
     p.off_xn = pl.off_xn;
     p.off_sort = pl.off_sort;
     p.off_bar = pl.off_bar;
+    p.trace = nullptr;
+    const char* trace_path = getenv("B200KM_TRACE");
+    if (trace_path && acc) {
+        cudaMalloc((void**)&p.trace, 256 * 8 * sizeof(unsigned long long));
+        cudaMemsetAsync(p.trace, 0, 256 * 8 * sizeof(unsigned long long), s);
+    }
     int64_t grid = p.num_tiles < kNumSMs ? p.num_tiles : kNumSMs;
     if (grid < 1) grid = 1;
     kmeans_fused_tc_kernel<<<(unsigned)grid, kThreads, pl.total, s>>>(tmX, tmC, p);
@@ -711,6 +825,19 @@ int tc_pass(TcWorkspace* ws, const float* X, int64_t n, int d, int k, const floa
     if (e != cudaSuccess) {
         snprintf(g_tc_err, sizeof(g_tc_err), "fused kernel launch failed: %s", cudaGetErrorString(e));
         return 1;
+    }
+    if (p.trace) {  // development aid: synchronous dump of CTA 0's per-tile event clocks
+        static unsigned long long host[256 * 8];
+        cudaStreamSynchronize(s);
+        cudaMemcpy(host, p.trace, sizeof(host), cudaMemcpyDeviceToHost);
+        cudaFree(p.trace);
+        if (FILE* f = fopen(trace_path, "w")) {
+            for (int i = 0; i < 256; ++i) {
+                for (int j = 0; j < 8; ++j) fprintf(f, "%llu ", host[i * 8 + j]);
+                fprintf(f, "\n");
+            }
+            fclose(f);
+        }
     }
     return 0;
 }
