@@ -206,12 +206,12 @@ int pick_path(b200km_handle* h, const float* X, int d, int k, bool with_acc, boo
 // One assignment (+ optional accumulation) pass on the chosen path.
 // labels/best may be workspace or caller buffers.  acc == nullptr -> assignment only.
 int run_pass(b200km_handle* h, bool use_tc, const float* X, int64_t n, int d, int k, const float* C,
-             int32_t* labels, float* best, double* acc, bool honor_done, cudaStream_t s) {
+             int32_t* labels, float* best, double* acc, bool honor_done, bool xn_compute, cudaStream_t s) {
     // the dominant kernel of the pass is bracketed by an event pair when profiling is on
     const bool rec = h->prof && h->prof_n < b200km_handle::kProfMax;
     if (rec) CU_TRY(cudaEventRecord(h->pev[2 * h->prof_n], s));
     if (use_tc) {
-        if (tc_pass(&h->tc, X, n, d, k, C, h->d_cnorm, labels, best, acc, h->d_state, honor_done, s))
+        if (tc_pass(&h->tc, X, n, d, k, C, h->d_cnorm, h->d_xnorm, xn_compute, labels, best, acc, h->d_state, honor_done, s))
             return fail("tcgen05 pass failed: %s", tc_last_error());
         if (rec) CU_TRY(cudaEventRecord(h->pev[2 * h->prof_n + 1], s));
         if (rec) h->prof_n++;
@@ -400,7 +400,7 @@ int b200km_fit(b200km_handle* h, const float* X, int64_t n_local, int d, int k, 
             CU_TRY(cudaEventSynchronize(h->ev[slot]));
             if (h->h_state[slot].done) break;
         }
-        if (run_pass(h, use_tc, X, n_local, d, k, h->d_C, h->d_labels, h->d_best, h->d_acc, true, s)) return 1;
+        if (run_pass(h, use_tc, X, n_local, d, k, h->d_C, h->d_labels, h->d_best, h->d_acc, true, it == 0, s)) return 1;
         if (h->nranks > 1)
             NCCL_TRY(g_nccl.AllReduce(h->d_acc, h->d_acc, (size_t)acc_len, ncclFloat64, ncclSum, h->comm, s));
         launch_finalize(h->d_C, k, d, h->d_cnorm, h->d_acc, h->d_shift, tol, h->d_state, s);
@@ -413,7 +413,7 @@ int b200km_fit(b200km_handle* h, const float* X, int64_t n_local, int d, int k, 
     double* d_inertia = h->d_acc + kd + k;
     if (inertia_out || labels_out) {
         int32_t* lab = labels_out ? labels_out : h->d_labels;
-        if (run_pass(h, use_tc, X, n_local, d, k, h->d_C, lab, h->d_best, nullptr, false, s)) return 1;
+        if (run_pass(h, use_tc, X, n_local, d, k, h->d_C, lab, h->d_best, nullptr, false, max_iter == 0, s)) return 1;
         CU_TRY(cudaMemsetAsync(d_inertia, 0, sizeof(double), s));
         launch_sum_best(h->d_best, n_local, d_inertia, s);
         h->launches += 1;
@@ -445,7 +445,7 @@ int b200km_lloyd_step(b200km_handle* h, const float* X, int64_t n, int d, int k,
     launch_prep(centroids, k, d, h->d_cnorm, h->d_acc, (int64_t)kd + k + 1, h->d_state, true, s);
     CU_TRY(cudaGetLastError());
     int32_t* lab = labels_out ? labels_out : h->d_labels;
-    if (n > 0 && run_pass(h, use_tc, X, n, d, k, centroids, lab, h->d_best, h->d_acc, false, s)) return 1;
+    if (n > 0 && run_pass(h, use_tc, X, n, d, k, centroids, lab, h->d_best, h->d_acc, false, true, s)) return 1;
     CU_TRY(cudaMemcpyAsync(sums_out, h->d_acc, sizeof(double) * kd, cudaMemcpyDeviceToDevice, s));
     CU_TRY(cudaMemcpyAsync(counts_out, h->d_acc + kd, sizeof(double) * k, cudaMemcpyDeviceToDevice, s));
     CU_TRY(cudaMemcpyAsync(inertia_out, h->d_acc + kd + k, sizeof(double), cudaMemcpyDeviceToDevice, s));
@@ -467,7 +467,7 @@ int b200km_predict(b200km_handle* h, const float* X, int64_t n, int d, const flo
     launch_prep(centroids, k, d, h->d_cnorm, nullptr, 0, h->d_state, false, s);
     CU_TRY(cudaGetLastError());
     float* best = min_dist_out ? min_dist_out : h->d_best;
-    return run_pass(h, use_tc, X, n, d, k, centroids, labels_out, best, nullptr, false, s);
+    return run_pass(h, use_tc, X, n, d, k, centroids, labels_out, best, nullptr, false, true, s);
 }
 
 int b200km_init_centroids(b200km_handle* h, const float* X, int64_t n_local, int d, int k, int mode,

@@ -16,8 +16,11 @@ int tc_max_k();
 size_t tc_workspace_bytes(int d, int k);
 // One fused pass: labels + best for every row; when acc != nullptr also the float64 per-cluster
 // sums / counts / inertia ([k*d | k | 1]) accumulated into acc.  Returns 0 on success.
+// xnorm: device [n] row norms; written by the pass when xn_compute, otherwise read (a fit computes them
+// in its first pass and reuses them in the later ones).
 int tc_pass(TcWorkspace* ws, const float* X, int64_t n, int d, int k, const float* C, const float* cnorm,
-            int32_t* labels, float* best, double* acc, IterState* st, bool honor_done, cudaStream_t s);
+            float* xnorm, bool xn_compute, int32_t* labels, float* best, double* acc, IterState* st,
+            bool honor_done, cudaStream_t s);
 const char* tc_last_error();
 void tc_free(TcWorkspace* ws);
 
