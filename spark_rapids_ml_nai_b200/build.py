@@ -12,6 +12,8 @@ NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
     "-Xcompiler", "-fPIC,-O2,-Wall", "--expt-relaxed-constexpr",
 ]
+if os.environ.get("B200KM_ENABLE_TRACE"):  # development builds: per-tile event clocks (tools/trace_view.py)
+    NVCC_FLAGS.append("-DB200KM_ENABLE_TRACE")
 
 
 def _stale(out, deps):

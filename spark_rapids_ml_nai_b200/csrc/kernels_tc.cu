@@ -39,7 +39,7 @@ constexpr int kTileM = 128;
 constexpr int kAtomBytes = kTileM * 128;  // one full K-atom of an X tile: 128 rows x 32 floats
 constexpr int kRing = 4;                  // TMEM ring slots for (x_hi | x_lo) atoms, 64 columns each
 constexpr int kRingCol0 = 256;            // ring occupies TMEM columns [256, 512)
-constexpr int kThreads = 512;
+constexpr int kThreads = 768;
 constexpr int kMaxSmem = 227 * 1024;
 constexpr int kMaxStages = 4;
 constexpr int kMaxD = 256;
@@ -64,7 +64,7 @@ struct TcParams {
     IterState* st;
     int honor_done;
     float tie_tol;
-    unsigned long long* trace;  // development aid (B200KM_TRACE): [256 tiles][8 events] clock64 of CTA 0
+    unsigned long long* trace;  // development aid (B200KM_TRACE): [256 tiles][16 events] clock64 of CTA 0
     // shared-memory offsets (bytes from the 1024-aligned base)
     int off_c, off_acc, off_cn, off_xn, off_bar;
 };
@@ -83,7 +83,8 @@ __device__ __forceinline__ void mbar_arrive_expect_tx(uint32_t bar, uint32_t byt
 }
 // Blocking wait: try_wait suspends the warp in hardware (up to the time hint) until the phase completes,
 // so a waiting role costs no issue slots (a software poll loop measured ~9000 instructions per tile).
-__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+// Not inlined: the kernel runs five instruction streams per SM and its hot code has to stay cache-resident.
+__device__ __noinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
     asm volatile(
         "{\n\t"
         ".reg .pred p;\n\t"
@@ -187,7 +188,9 @@ __device__ __forceinline__ uint32_t tf32_trunc(uint32_t bits) { return bits & 0x
 __device__ __forceinline__ uint32_t tf32_round(uint32_t bits) { return (bits + 0x1000u) & 0xFFFFE000u; }
 
 __device__ __forceinline__ void trace_ev(const TcParams& p, int64_t it, int ev) {
-    if (p.trace && blockIdx.x == 0 && it < 256) p.trace[it * 8 + ev] = (unsigned long long)clock64();
+#ifdef B200KM_ENABLE_TRACE
+    if (p.trace && blockIdx.x == 0 && it < 256) p.trace[it * 16 + ev] = (unsigned long long)clock64();
+#endif
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -288,10 +291,11 @@ __global__ void __launch_bounds__(kThreads, 1)
     if (p.honor_done && p.st->done) return;
 
     extern __shared__ uint8_t smem_raw[];
-    __shared__ int s_hist[4][kHist];  // per-assign-warp label histograms, then offsets
+    __shared__ int s_hist[2][4][kHist];  // per assign group: per-warp label histograms, then offsets
+    __shared__ int s_cand[2][kTileM][4];  // per assign group: candidate centroids of near-tie rows
     __shared__ int s_base[2][kHist];  // start of every label's run in the sorted order (double-buffered)
-    __shared__ int s_perm[2][kTileM];   // sorted position -> row offset in a full atom (r*128 | swizzle) | label<<16
-    __shared__ int s_permT[2][kTileM];  // same for the narrow tail atom (row pitch 64 / 32 bytes)
+    __shared__ int s_perm[2][kTileM + 8];   // sorted position -> row offset in a full atom (r*128 | swizzle) | label<<16
+    __shared__ int s_permT[2][kTileM + 8];  // same for the narrow tail atom (row pitch 64 / 32 bytes)
     // pointer arithmetic (not an integer round trip) keeps the shared address space visible to the compiler
     uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
     const uint32_t smem_base = smem_u32(smem);
@@ -316,7 +320,7 @@ __global__ void __launch_bounds__(kThreads, 1)
     if (threadIdx.x == 0) {
         for (int s = 0; s < kMaxStages; ++s) {
             mbar_init(x_full0 + 8u * s, 1);
-            mbar_init(x_empty0 + 8u * s, 4);
+            mbar_init(x_empty0 + 8u * s, p.acc ? 8 : 4);
             mbar_init(xn_full0 + 8u * s, 4);
         }
         for (int s = 0; s < kRing; ++s) {
@@ -327,7 +331,7 @@ __global__ void __launch_bounds__(kThreads, 1)
             mbar_init(d_full0 + 8u * s, 1);
             mbar_init(d_empty0 + 8u * s, 4);
             mbar_init(s_full0 + 8u * s, 4);
-            mbar_init(s_empty0 + 8u * s, 4);
+            mbar_init(s_empty0 + 8u * s, 8);
         }
         mbar_init(c_full, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -336,6 +340,24 @@ __global__ void __launch_bounds__(kThreads, 1)
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)),
                      "r"(512));
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::);
+    }
+    {
+        // shared state every role relies on, written once by all threads before the first barrier
+        float* cn_init = (float*)(smem + p.off_cn);
+#pragma unroll 1
+        for (int j = threadIdx.x; j < p.k_pad; j += kThreads) cn_init[j] = (j < p.k) ? p.cnorm[j] : FLT_MAX;
+        if (p.acc) {
+            double* sacc_init = (double*)(smem + p.off_acc);
+#pragma unroll 1
+            for (int i = threadIdx.x; i < p.k * p.d + p.k; i += kThreads) sacc_init[i] = 0.0;
+        }
+#pragma unroll 1
+        for (int i = threadIdx.x; i < 2 * 4 * kHist; i += kThreads) (&s_hist[0][0][0])[i] = 0;
+#pragma unroll 1
+        for (int i = threadIdx.x; i < 2 * (kTileM + 8); i += kThreads) {
+            (&s_perm[0][0])[i] = 0;
+            (&s_permT[0][0])[i] = 0;
+        }
     }
     tc_fence_before();
     __syncthreads();
@@ -381,6 +403,8 @@ __global__ void __launch_bounds__(kThreads, 1)
         // D[:, 0:2k) += x_lo.[c_hi;c_lo]^T, i.e. all four partial products of (x_hi+x_lo).(c_hi+c_lo).
         const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(kTileM >> 4) << 24) |
                                ((uint32_t)(dcols >> 3) << 17);
+        const uint64_t desc_full = make_b_desc(smem_base + p.off_c, 128);
+        const uint64_t desc_tail = make_b_desc(smem_base + p.off_c + p.n_full * c_block, p.tail_cols ? p.tail_cols * 4 : 128);
         mbar_wait(c_full, 0);
         int64_t it = 0;   // tile counter
         int64_t ait = 0;  // atom counter (ring position)
@@ -388,35 +412,40 @@ __global__ void __launch_bounds__(kThreads, 1)
             const int db = (int)(it % ND);
             mbar_wait(d_empty0 + 8u * db, (uint32_t)(((it / ND) & 1) ^ 1));
             tc_fence_after();
+            if (lane == 0) trace_ev(p, it, 8);
             const uint32_t d_tmem = tmem_base + (uint32_t)(db * dcols);
             for (int a = 0; a < n_atoms; ++a, ++ait) {
                 const int slot = (int)(ait % kRing);
                 mbar_wait(a_full0 + 8u * slot, (uint32_t)((ait / kRing) & 1));
                 tc_fence_after();
+                if (lane == 0 && a == 0) trace_ev(p, it, 9);
+                if (lane == 0 && a == n_atoms - 1) trace_ev(p, it, 10);
                 const bool full = a < p.n_full;
-                const int row_bytes = full ? 128 : p.tail_cols * 4;
                 const int ksteps = full ? 4 : p.tail_cols >> 3;
                 const uint32_t a_hi = tmem_base + (uint32_t)(kRingCol0 + slot * 64);
-                const uint32_t a_lo = a_hi + 32;
-                const uint32_t b_hi = smem_base + p.off_c + a * c_block;  // tail block follows the full ones
-                const uint32_t b_lo = b_hi + p.k_pad * row_bytes;
-                for (int kk = 0; kk < ksteps; ++kk) {
-                    const uint64_t dh = make_b_desc(b_hi + kk * 32, row_bytes);
-                    if (stacked) {
-                        if (elect_one()) mma_tf32_ts(d_tmem, a_hi + 8 * kk, dh, idesc, (a | kk) != 0);
-                        if (elect_one()) mma_tf32_ts(d_tmem, a_lo + 8 * kk, dh, idesc, 1);
-                    } else {
-                        const uint64_t dl = make_b_desc(b_lo + kk * 32, row_bytes);
-                        if (elect_one()) mma_tf32_ts(d_tmem, a_lo + 8 * kk, dl, idesc, (a | kk) != 0);
-                        if (elect_one()) mma_tf32_ts(d_tmem, a_lo + 8 * kk, dh, idesc, 1);
-                        if (elect_one()) mma_tf32_ts(d_tmem, a_hi + 8 * kk, dl, idesc, 1);
-                        if (elect_one()) mma_tf32_ts(d_tmem, a_hi + 8 * kk, dh, idesc, 1);
+                // descriptors differ between K-steps only in the start-address field: +32 B = +2 units
+                const uint64_t dh0 = full ? desc_full + (uint64_t)(a * (c_block >> 4)) : desc_tail;
+                const uint64_t dl0 = dh0 + (uint64_t)((p.k_pad * (full ? 128 : p.tail_cols * 4)) >> 4);
+                if (elect_one()) {
+#pragma unroll
+                    for (int kk = 0; kk < 4; ++kk) {
+                        if (kk < ksteps) {
+                            if (stacked) {
+                                mma_tf32_ts(d_tmem, a_hi + 8 * kk, dh0 + 2 * kk, idesc, (a | kk) != 0);
+                                mma_tf32_ts(d_tmem, a_hi + 32 + 8 * kk, dh0 + 2 * kk, idesc, 1);
+                            } else {
+                                mma_tf32_ts(d_tmem, a_hi + 32 + 8 * kk, dl0 + 2 * kk, idesc, (a | kk) != 0);
+                                mma_tf32_ts(d_tmem, a_hi + 32 + 8 * kk, dh0 + 2 * kk, idesc, 1);
+                                mma_tf32_ts(d_tmem, a_hi + 8 * kk, dl0 + 2 * kk, idesc, 1);
+                                mma_tf32_ts(d_tmem, a_hi + 8 * kk, dh0 + 2 * kk, idesc, 1);
+                            }
+                        }
                     }
-                }
-                if (elect_one()) tc_commit(a_empty0 + 8u * slot);
-                if (a == n_atoms - 1) {
-                    if (elect_one()) tc_commit(d_full0 + 8u * db);
-                    if (lane == 0) trace_ev(p, it, 3);
+                    tc_commit(a_empty0 + 8u * slot);
+                    if (a == n_atoms - 1) {
+                        tc_commit(d_full0 + 8u * db);
+                        trace_ev(p, it, 3);
+                    }
                 }
                 __syncwarp();
             }
@@ -448,28 +477,29 @@ __global__ void __launch_bounds__(kThreads, 1)
             __syncwarp();
             if (lane == 0) mbar_arrive(xn_full0 + 8u * s);
             if (threadIdx.x == 128) trace_ev(p, it, 2);
+            if (lane == 0 && q < 2) trace_ev(p, it, 12 + q);
         }
-    } else if (warp >= 8 && warp < 12) {
+    } else if (warp >= 8 && warp < 16) {
         // ======================================== assign ========================================
+        // Two groups of four warps take alternate tiles (group g owns the D buffer and the sort buffer of
+        // its parity), so the argmin / refine / sort latency of one tile overlaps the next tile's.
+        const int g = (warp - 8) >> 2;
+        if (g < ND) {
         const int q = warp & 3;
         const int row = q * 32 + lane;
-        const int et = threadIdx.x - 8 * 32;  // 0..127 within the group
+        const int et = threadIdx.x - (8 + 4 * g) * 32;  // 0..127 within the group
+        const int bar_id = 1 + g;
         float* cn_s = (float*)(smem + p.off_cn);
         float* xn_s = (float*)(smem + p.off_xn);
-        double* sacc = (double*)(smem + p.off_acc);
-        const int acc_n = p.k * p.d + p.k;
-        for (int j = et; j < p.k_pad; j += 128) cn_s[j] = (j < p.k) ? p.cnorm[j] : FLT_MAX;
-        if (p.acc)
-            for (int i = et; i < acc_n; i += 128) sacc[i] = 0.0;
-        for (int i = et; i < 4 * kHist; i += 128) (&s_hist[0][0])[i] = 0;
         const float cmax = p.st->cnorm_max;
-        named_bar_sync(1, 128);
+        int (*hist)[kHist] = s_hist[g];
 
         double inert = 0.0;
-        int64_t it = 0;
-        for (int64_t tile = first_tile; tile < p.num_tiles; tile += tile_step, ++it) {
+        for (int64_t it = g;; it += ND) {
+            const int64_t tile = first_tile + it * tile_step;
+            if (tile >= p.num_tiles) break;
             const int s = (int)(it % S);
-            const int db = (int)(it % ND);
+            const int db = g;
             const int sb = (int)(it & 1);
             const int64_t grow = tile * kTileM + row;
             const bool valid = grow < p.n;
@@ -506,9 +536,10 @@ __global__ void __launch_bounds__(kThreads, 1)
             const float band = p.tie_tol * (xn + cmax);
             const bool amb = valid && p.k > 1 && (b2 - b1) < band;
             unsigned m = __ballot_sync(0xffffffffu, amb);
-            // near-tie rows: second look at the scores to list the candidates inside the band (up to 4)
-            int ncand = 0, cand0 = 0, cand1 = 0, cand2 = 0, cand3 = 0;
+            // near-tie rows: a second look at the scores lists the candidates inside the band (first 4 kept)
+            int ncand = 0;
             if (m) {
+#pragma unroll 1
                 for (int c0 = 0; c0 < p.k; c0 += 16) {
                     uint32_t r[16], r2[16];
                     tmem_ld16(taddr + c0, r);
@@ -520,10 +551,7 @@ __global__ void __launch_bounds__(kThreads, 1)
                         if (stacked) dot += __uint_as_float(r2[j]);
                         const float sc = fmaf(-2.f, dot, cn_s[c0 + j]);
                         if (amb && (c0 + j) < p.k && (sc - b1) < band) {
-                            if (ncand == 0) cand0 = c0 + j;
-                            else if (ncand == 1) cand1 = c0 + j;
-                            else if (ncand == 2) cand2 = c0 + j;
-                            else if (ncand == 3) cand3 = c0 + j;
+                            if (ncand < 4) s_cand[g][et][ncand] = c0 + j;
                             ++ncand;
                         }
                     }
@@ -542,13 +570,11 @@ __global__ void __launch_bounds__(kThreads, 1)
                 m &= m - 1;
                 const int rr = q * 32 + src;
                 const int nc = __shfl_sync(0xffffffffu, ncand, src);
-                const int c_0 = __shfl_sync(0xffffffffu, cand0, src), c_1 = __shfl_sync(0xffffffffu, cand1, src);
-                const int c_2 = __shfl_sync(0xffffffffu, cand2, src), c_3 = __shfl_sync(0xffffffffu, cand3, src);
                 const int total = nc <= 4 ? nc : p.k;  // more than 4 candidates: scan every centroid
                 double bd = DBL_MAX;
                 int bi = 0;
                 for (int t = 0; t < total; ++t) {
-                    const int j = nc <= 4 ? (t == 0 ? c_0 : t == 1 ? c_1 : t == 2 ? c_2 : c_3) : t;
+                    const int j = nc <= 4 ? s_cand[g][rr][t] : t;
                     const float* c = p.C + (size_t)j * p.d;
                     double sum = 0.0;
                     for (int i = lane; i < p.d; i += 32) {
@@ -582,15 +608,15 @@ __global__ void __launch_bounds__(kThreads, 1)
                 const int bin = valid ? label : p.k;
                 const unsigned peers = __match_any_sync(0xffffffffu, bin);
                 const int rank_w = __popc(peers & ((1u << lane) - 1u));
-                if (rank_w == 0) s_hist[q][bin] = __popc(peers);
-                named_bar_sync(1, 128);
+                if (rank_w == 0) hist[q][bin] = __popc(peers);
+                named_bar_sync(bar_id, 128);
                 if (q == 0) {
                     // one warp turns the 4 per-warp histograms into offsets; lane owns `per` consecutive bins
                     const int per = (bins + 31) >> 5;
                     const int b0 = lane * per;
                     int lane_total = 0;
                     for (int bb = b0; bb < b0 + per && bb < bins; ++bb)
-                        lane_total += s_hist[0][bb] + s_hist[1][bb] + s_hist[2][bb] + s_hist[3][bb];
+                        lane_total += hist[0][bb] + hist[1][bb] + hist[2][bb] + hist[3][bb];
                     int incl = lane_total;
 #pragma unroll
                     for (int o = 1; o < 32; o <<= 1) {
@@ -599,29 +625,29 @@ __global__ void __launch_bounds__(kThreads, 1)
                     }
                     int run = incl - lane_total;
                     for (int bb = b0; bb < b0 + per && bb < bins; ++bb) {
-                        const int h0 = s_hist[0][bb], h1 = s_hist[1][bb], h2 = s_hist[2][bb], h3 = s_hist[3][bb];
+                        const int h0 = hist[0][bb], h1 = hist[1][bb], h2 = hist[2][bb], h3 = hist[3][bb];
                         s_base[sb][bb] = run;
-                        s_hist[0][bb] = run;
-                        s_hist[1][bb] = run + h0;
-                        s_hist[2][bb] = run + h0 + h1;
-                        s_hist[3][bb] = run + h0 + h1 + h2;
-                        const int tot = h0 + h1 + h2 + h3;
-                        if (bb < p.k && tot) sacc[p.k * p.d + bb] += (double)tot;  // sole owner of the counts
-                        run += tot;
+                        hist[0][bb] = run;
+                        hist[1][bb] = run + h0;
+                        hist[2][bb] = run + h0 + h1;
+                        hist[3][bb] = run + h0 + h1 + h2;
+                        run += h0 + h1 + h2 + h3;
                     }
                     if (lane == 31) s_base[sb][bins] = run;
                 }
-                named_bar_sync(1, 128);
+                named_bar_sync(bar_id, 128);
                 {
-                    // sorted position -> row offset inside a full atom (r*128 | swizzle) and the label
-                    const int pos = s_hist[q][bin] + rank_w;
-                    s_perm[sb][pos] = (row << 7) | ((row & 7) << 4) | (bin << 16);
-                    if (p.tail_cols == 16) s_permT[sb][pos] = (row << 6) | (((row >> 1) & 3) << 4) | (bin << 16);
-                    else if (p.tail_cols == 8) s_permT[sb][pos] = (row << 5) | (((row >> 2) & 1) << 4) | (bin << 16);
+                    // sorted position -> row offset inside an atom (r*pitch | swizzle bits), a last-of-run flag
+                    // (bit 16) and the label (bits 17+)
+                    const int pos = hist[q][bin] + rank_w;
+                    const int meta = ((pos == s_base[sb][bin + 1] - 1) ? (1 << 16) : 0) | (bin << 17);
+                    s_perm[sb][pos] = (row << 7) | ((row & 7) << 4) | meta;
+                    if (p.tail_cols == 16) s_permT[sb][pos] = (row << 6) | (((row >> 1) & 3) << 4) | meta;
+                    else if (p.tail_cols == 8) s_permT[sb][pos] = (row << 5) | (((row >> 2) & 1) << 4) | meta;
                 }
                 __syncwarp();
-                for (int bb = lane; bb < bins; bb += 32) s_hist[q][bb] = 0;  // own row only: ready for the next tile
-                named_bar_sync(1, 128);
+                for (int bb = lane; bb < bins; bb += 32) hist[q][bb] = 0;  // own row only: ready for the next tile
+                __syncwarp();  // the warp's s_perm writes precede its arrival; the update group waits for all four
                 if (et == 0) trace_ev(p, it, 6);
                 if (lane == 0) mbar_arrive(s_full0 + 8u * sb);
             } else {
@@ -629,84 +655,160 @@ __global__ void __launch_bounds__(kThreads, 1)
                 if (lane == 0) mbar_arrive(x_empty0 + 8u * s);
             }
         }
-
         if (p.acc) {
-            named_bar_sync(1, 128);
-            for (int i = p.k * p.d + et; i < acc_n; i += 128) {
-                const double v = sacc[i];
-                if (v != 0.0) atomicAdd(&p.acc[i], v);
-            }
 #pragma unroll
             for (int o = 16; o > 0; o >>= 1) inert += __shfl_xor_sync(0xffffffffu, inert, o);
-            if (lane == 0 && inert != 0.0) atomicAdd(&p.acc[acc_n], inert);
+            if (lane == 0 && inert != 0.0) atomicAdd(&p.acc[p.k * p.d + p.k], inert);
         }
-    } else if (warp >= 12 && p.acc) {
+        }
+    } else if (warp >= 16 && p.acc) {
         // ======================================== update ========================================
-        // Warp q owns the labels [q*k/4, (q+1)*k/4), i.e. one contiguous range of sorted positions; lane =
-        // float4 column chunk.  Consecutive equal-label rows are summed in FP32 registers and flushed once
-        // per run with a plain float64 read-modify-write: every (label, column) has exactly one owner, so
-        // no atomics are needed.
-        const int q = warp & 3;
-        const int ut = threadIdx.x - 12 * 32;
+        // Eight warps; warp u owns the labels [u*k/8, (u+1)*k/8) for the whole kernel, i.e. one contiguous
+        // range of each tile's label-sorted rows; lane = float4 column chunk.  No other thread ever touches
+        // an owner's (label, column) sums, so no atomics are needed anywhere in the tile loop.
+        const int u = warp - 16;
+        const int ut = threadIdx.x - 16 * 32;
         double* sacc = (double*)(smem + p.off_acc);
         const int nchunks = p.d >> 2;
-        const int l_lo = (q * p.k) >> 2, l_hi = ((q + 1) * p.k) >> 2;
-        int64_t it = 0;
-        for (int64_t tile = first_tile; tile < p.num_tiles; tile += tile_step, ++it) {
-            const int s = (int)(it % S);
-            const int sb = (int)(it & 1);
-            mbar_wait(s_full0 + 8u * sb, (uint32_t)((it >> 1) & 1));
-            mbar_wait(x_full0 + 8u * s, (uint32_t)((it / S) & 1));
-            const uint8_t* stage = smem + (size_t)s * stage_bytes;
-            for (int ch = lane; ch < nchunks; ch += 32) {
-                // lane = float4 column chunk; full atoms use the packed (r*128 | swz) word, the narrow tail its own
-                const int a = ch >> 3;
-                const bool tail = a >= p.n_full;
-                const uint8_t* colp = stage + (tail ? p.n_full : a) * kAtomBytes;
-                const int c16 = (tail ? (ch - p.n_full * 8) : (ch & 7)) << 4;
+        const int l_lo = (u * p.k) >> 3, l_hi = ((u + 1) * p.k) >> 3;
+        const bool reg_path = p.k <= 32 && nchunks <= 32;
+        if (reg_path) {
+            // k <= 32: at most 4 owned labels.  Their FP32 sums live in registers and are folded into the
+            // float64 shared accumulators every 8 tiles.  The row loop is branch-free inside a label
+            // (predicated adds): a single warp per scheduler pays ~20 cycles for every taken branch.
+            const bool active = lane < nchunks;
+            const int ch = active ? lane : 0;
+            const int a = ch >> 3;
+            const bool tail = a >= p.n_full;
+            const int col_off = (tail ? p.n_full : a) * kAtomBytes;
+            const int c16 = (tail ? (ch - p.n_full * 8) : (ch & 7)) << 4;
+            float4 acc[4];
+            int cnt[4];
+#pragma unroll
+            for (int li = 0; li < 4; ++li) {
+                acc[li] = make_float4(0.f, 0.f, 0.f, 0.f);
+                cnt[li] = 0;
+            }
+            auto fold = [&]() {
+#pragma unroll
+                for (int li = 0; li < 4; ++li) {
+                    if (l_lo + li < l_hi) {
+                        if (active) {
+                            double2* dst = reinterpret_cast<double2*>(sacc + (size_t)(l_lo + li) * p.d + ch * 4);
+                            double2 a0 = dst[0], a1 = dst[1];
+                            a0.x += (double)acc[li].x;
+                            a0.y += (double)acc[li].y;
+                            a1.x += (double)acc[li].z;
+                            a1.y += (double)acc[li].w;
+                            dst[0] = a0;
+                            dst[1] = a1;
+                        }
+                        if (lane == 0) sacc[p.k * p.d + l_lo + li] += (double)cnt[li];
+                        acc[li] = make_float4(0.f, 0.f, 0.f, 0.f);
+                        cnt[li] = 0;
+                    }
+                }
+            };
+            int64_t it = 0;
+            for (int64_t tile = first_tile; tile < p.num_tiles; tile += tile_step, ++it) {
+                const int s = (int)(it % S);
+                const int sb = (int)(it & 1);
+                mbar_wait(s_full0 + 8u * sb, (uint32_t)((it >> 1) & 1));
+                mbar_wait(x_full0 + 8u * s, (uint32_t)((it / S) & 1));
+                if (ut == 0) trace_ev(p, it, 11);
+                const uint8_t* colp = smem + (size_t)s * stage_bytes + col_off;
                 const int* perm = tail ? s_permT[sb] : s_perm[sb];
                 int beg = s_base[sb][l_lo];
-                for (int l = l_lo; l < l_hi; ++l) {
-                    const int end = s_base[sb][l + 1];
-                    if (end > beg) {
-                        float4 run = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+                for (int li = 0; li < 4; ++li) {
+                    if (l_lo + li < l_hi) {
+                        const int end = s_base[sb][l_lo + li + 1];
+                        float4 r = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll 1
                         for (int base = beg; base < end; base += 4) {
+                            int w[4];
                             float4 v[4];
 #pragma unroll
-                            for (int j = 0; j < 4; ++j) {
-                                v[j] = make_float4(0.f, 0.f, 0.f, 0.f);
-                                if (base + j < end)
-                                    v[j] = *reinterpret_cast<const float4*>(colp + ((perm[base + j] & 0xFFFF) ^ c16));
-                            }
+                            for (int j = 0; j < 4; ++j) w[j] = perm[base + j];  // past `end`: stale but valid offsets
+#pragma unroll
+                            for (int j = 0; j < 4; ++j)
+                                v[j] = *reinterpret_cast<const float4*>(colp + ((w[j] & 0xFFFF) ^ c16));
 #pragma unroll
                             for (int j = 0; j < 4; ++j) {
-                                run.x += v[j].x;
-                                run.y += v[j].y;
-                                run.z += v[j].z;
-                                run.w += v[j].w;
+                                if (base + j < end) {
+                                    r.x += v[j].x;
+                                    r.y += v[j].y;
+                                    r.z += v[j].z;
+                                    r.w += v[j].w;
+                                }
                             }
                         }
-                        double2* dst = reinterpret_cast<double2*>(sacc + (size_t)l * p.d + ch * 4);
-                        double2 a0 = dst[0], a1 = dst[1];
-                        a0.x += (double)run.x;
-                        a0.y += (double)run.y;
-                        a1.x += (double)run.z;
-                        a1.y += (double)run.w;
-                        dst[0] = a0;
-                        dst[1] = a1;
+                        acc[li].x += r.x;
+                        acc[li].y += r.y;
+                        acc[li].z += r.z;
+                        acc[li].w += r.w;
+                        cnt[li] += end - beg;
+                        beg = end;
                     }
-                    beg = end;
+                }
+                __syncwarp();
+                if (lane == 0) {
+                    mbar_arrive(s_empty0 + 8u * sb);
+                    mbar_arrive(x_empty0 + 8u * s);
+                }
+                if (ut == 0) trace_ev(p, it, 7);
+                if ((it & 7) == 7 || tile + tile_step >= p.num_tiles) fold();  // single (rare) fold site
+            }
+        } else {
+            // general shapes: flat walk over the owned range, run sums flushed at the last row of each run
+            int64_t it = 0;
+            for (int64_t tile = first_tile; tile < p.num_tiles; tile += tile_step, ++it) {
+                const int s = (int)(it % S);
+                const int sb = (int)(it & 1);
+                mbar_wait(s_full0 + 8u * sb, (uint32_t)((it >> 1) & 1));
+                mbar_wait(x_full0 + 8u * s, (uint32_t)((it / S) & 1));
+                const uint8_t* stage = smem + (size_t)s * stage_bytes;
+                const int pb = s_base[sb][l_lo], pe = s_base[sb][l_hi];
+                for (int ch = lane; ch < nchunks; ch += 32) {
+                    const int a = ch >> 3;
+                    const bool tail = a >= p.n_full;
+                    const uint8_t* colp = stage + (tail ? p.n_full : a) * kAtomBytes;
+                    const int c16 = (tail ? (ch - p.n_full * 8) : (ch & 7)) << 4;
+                    const int* perm = tail ? s_permT[sb] : s_perm[sb];
+                    float4 r = make_float4(0.f, 0.f, 0.f, 0.f);
+                    for (int pos = pb; pos < pe; ++pos) {
+                        const int w = perm[pos];
+                        const float4 v = *reinterpret_cast<const float4*>(colp + ((w & 0xFFFF) ^ c16));
+                        r.x += v.x;
+                        r.y += v.y;
+                        r.z += v.z;
+                        r.w += v.w;
+                        if (w & (1 << 16)) {  // last row of this label's run (warp-uniform)
+                            double2* dst = reinterpret_cast<double2*>(sacc + (size_t)(w >> 17) * p.d + ch * 4);
+                            double2 a0 = dst[0], a1 = dst[1];
+                            a0.x += (double)r.x;
+                            a0.y += (double)r.y;
+                            a1.x += (double)r.z;
+                            a1.y += (double)r.w;
+                            dst[0] = a0;
+                            dst[1] = a1;
+                            r = make_float4(0.f, 0.f, 0.f, 0.f);
+                        }
+                    }
+                }
+                for (int l = l_lo + lane; l < l_hi; l += 32)
+                    sacc[p.k * p.d + l] += (double)(s_base[sb][l + 1] - s_base[sb][l]);
+                __syncwarp();
+                if (lane == 0) {
+                    mbar_arrive(s_empty0 + 8u * sb);
+                    mbar_arrive(x_empty0 + 8u * s);
                 }
             }
-            __syncwarp();
-            if (lane == 0) {
-                mbar_arrive(s_empty0 + 8u * sb);
-                mbar_arrive(x_empty0 + 8u * s);
-            }
-            if (ut == 0) trace_ev(p, it, 7);
         }
-        named_bar_sync(2, 128);
-        for (int i = ut; i < p.k * p.d; i += 128) {
+        named_bar_sync(3, 256);
+        const int acc_n = p.k * p.d + p.k;
+#pragma unroll 1
+        for (int i = ut; i < acc_n; i += 256) {
             const double v = sacc[i];
             if (v != 0.0) atomicAdd(&p.acc[i], v);
         }
@@ -761,7 +863,7 @@ int encode_2d(CUtensorMap* tm, const void* base, uint64_t cols, uint64_t rows, u
     return 0;
 }
 
-constexpr int kStaticSmem = 9 * 1024;  // upper bound of the kernel's static shared arrays
+constexpr int kStaticSmem = 17 * 1024;  // upper bound of the kernel's static shared arrays
 
 struct Plan {
     int k_pad, n_full, tail_cols, d_pad, num_stages, num_d, stage_bytes;
@@ -916,8 +1018,8 @@ int tc_pass(TcWorkspace* ws, const float* X, int64_t n, int d, int k, const floa
     p.trace = nullptr;
     const char* trace_path = getenv("B200KM_TRACE");
     if (trace_path && acc) {
-        cudaMalloc((void**)&p.trace, 256 * 8 * sizeof(unsigned long long));
-        cudaMemsetAsync(p.trace, 0, 256 * 8 * sizeof(unsigned long long), s);
+        cudaMalloc((void**)&p.trace, 256 * 16 * sizeof(unsigned long long));
+        cudaMemsetAsync(p.trace, 0, 256 * 16 * sizeof(unsigned long long), s);
     }
     int64_t grid = p.num_tiles < kNumSMs ? p.num_tiles : kNumSMs;
     if (grid < 1) grid = 1;
@@ -928,13 +1030,13 @@ int tc_pass(TcWorkspace* ws, const float* X, int64_t n, int d, int k, const floa
         return 1;
     }
     if (p.trace) {  // development aid: synchronous dump of CTA 0's per-tile event clocks
-        static unsigned long long host[256 * 8];
+        static unsigned long long host[256 * 16];
         cudaStreamSynchronize(s);
         cudaMemcpy(host, p.trace, sizeof(host), cudaMemcpyDeviceToHost);
         cudaFree(p.trace);
         if (FILE* f = fopen(trace_path, "w")) {
             for (int i = 0; i < 256; ++i) {
-                for (int j = 0; j < 8; ++j) fprintf(f, "%llu ", host[i * 8 + j]);
+                for (int j = 0; j < 16; ++j) fprintf(f, "%llu ", host[i * 16 + j]);
                 fprintf(f, "\n");
             }
             fclose(f);
