@@ -130,6 +130,29 @@ int b200km_init_centroids(b200km_handle* h, const float* X, int64_t n_local, int
                           int mode, uint64_t seed, double oversampling, float* centroids_out,
                           void* stream);
 
+/* Nearest-centroid labels for callers that cannot allocate device memory: a transform task whose GPU
+ * memory is already owned by another pool, a latency-bound serving thread (cudaMalloc may serialise the
+ * device), or anything that must not fail for lack of memory.  It needs no handle and calls no
+ * cudaMalloc / cudaFree or allocating library routine: its scratch (row and centroid norms, distances,
+ * the near-tie work list) is a fixed array inside the loaded module, held by every GPU that loads the
+ * library until the process exits (about 0.8 MB).  Limits: n <= B200KM_STATIC_MAX_ROWS rows and
+ * k <= B200KM_STATIC_MAX_K centroids per call; larger sizes are refused with an error (split the batch).
+ * X, centroids and labels_out are device pointers on the CURRENT device; work is enqueued on `stream`.
+ * The first call on each device resolves the array's address (cudaGetSymbolAddress) - make that call
+ * before any stream capture begins.  All calls share the one array, which keeps the last call's
+ * contents: the entry point clears the part that has to start at zero, but two calls that overlap on the
+ * GPU (different streams, or threads) race on it - serialise them.  Labels follow the same rule as
+ * b200km_predict (FP32 scores, near-ties re-decided in float64, lowest index wins ties).
+ * This entry point has no counterpart in the reference. */
+#define B200KM_STATIC_MAX_ROWS 65536
+#define B200KM_STATIC_MAX_K 1024
+int b200km_predict_static(const float* X, int64_t n, int d, const float* centroids, int k,
+                          int32_t* labels_out, void* stream);
+
+/* Message for the last failing b200km_predict_static call on this thread.  No counterpart in the
+ * reference. */
+const char* b200km_static_last_error(void);
+
 #ifdef __cplusplus
 }
 #endif

@@ -39,6 +39,9 @@ _SIGNATURES = {
                                      _c.c_void_p, _c.c_void_p, _c.c_void_p, _c.c_void_p, _c.c_void_p]),
     "b200km_predict": (_c.c_int, [_c.c_void_p, _c.c_void_p, _c.c_int64, _c.c_int, _c.c_void_p, _c.c_int,
                                   _c.c_void_p, _c.c_void_p, _c.c_void_p]),
+    "b200km_predict_static": (_c.c_int, [_c.c_void_p, _c.c_int64, _c.c_int, _c.c_void_p, _c.c_int, _c.c_void_p,
+                                         _c.c_void_p]),
+    "b200km_static_last_error": (_c.c_char_p, []),
     "b200km_init_centroids": (_c.c_int, [_c.c_void_p, _c.c_void_p, _c.c_int64, _c.c_int, _c.c_int, _c.c_int,
                                          _c.c_uint64, _c.c_double, _c.c_void_p, _c.c_void_p]),
 }
@@ -228,6 +231,32 @@ class Handle:
         _check(load().b200km_init_centroids(self._h, X.data_ptr(), n, d, k, mode, seed, float(oversampling),
                                             out.data_ptr(), _stream_ptr(stream)))
         return out
+
+
+STATIC_MAX_ROWS, STATIC_MAX_K = 65536, 1024
+
+
+def predict_static(X, centroids, out=None, stream=None):
+    """Labels through ``b200km_predict_static``: no handle, no allocation inside the library (the output
+    tensor is the caller's).  For callers that cannot allocate device memory; at most STATIC_MAX_ROWS rows
+    and STATIC_MAX_K centroids per call, calls must not overlap on the GPU.  The tensors must live on the
+    current CUDA device."""
+    import torch
+
+    dev = torch.cuda.current_device()
+    _check_tensor(X, "X", torch.float32, dev)
+    _check_tensor(centroids, "centroids", torch.float32, dev)
+    n, d = X.shape
+    k, d2 = centroids.shape
+    if d2 != d:
+        raise ValueError(f"centroids have {d2} columns, X has {d}")
+    labels = out if out is not None else torch.empty(n, dtype=torch.int32, device=X.device)
+    _check_tensor(labels, "labels", torch.int32, dev)
+    lib = load()
+    rc = lib.b200km_predict_static(X.data_ptr(), n, d, centroids.data_ptr(), k, labels.data_ptr(), _stream_ptr(stream))
+    if rc != 0:
+        raise RuntimeError("b200km: " + lib.b200km_static_last_error().decode("utf-8", "replace"))
+    return labels
 
 
 def tc_supported(d: int, k: int, with_update: bool = True) -> bool:
