@@ -238,8 +238,14 @@ def main():
     if kern_n > 0:
         kms = kern_ms / kern_n
         achieved = (4.0 * d * n_local) / (kms * 1e-3) / 1e9
+        traffic = None
+        tpath = os.path.join(ROOT, "profiles", "r01_traffic.json")
+        if path == "tc" and os.path.exists(tpath):
+            t = json.load(open(tpath))["kmeans_fused_tc"]
+            if (t["d"], t["k"]) == (d, k):  # bytes per row from the committed ncu capture, scaled to this launch
+                traffic = (t["dram_bytes_read"] + t["dram_bytes_write"]) / t["rows"] * n_local
         roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                    "traffic": None, "kernel": "kmeans_fused_tc" if path == "tc" else "assign_ffma_kernel",
+                    "traffic": traffic, "kernel": "kmeans_fused_tc" if path == "tc" else "assign_ffma_kernel",
                     "kernel_ms": kms, "launches_timed": kern_n, "peak_source": peak_src,
                     "algorithmic_bytes_per_launch": 4.0 * d * n_local}
 
