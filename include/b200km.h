@@ -37,7 +37,9 @@ typedef struct b200km_handle b200km_handle;
 /* kernel path selectors for b200km_set_path (diagnostics / tests) */
 #define B200KM_PATH_AUTO 0
 #define B200KM_PATH_FFMA 1 /* generic SIMT FFMA tiles + separate update pass */
-#define B200KM_PATH_TC 2   /* tcgen05/TMEM/TMA 3xTF32 fused pass (where the shape allows) */
+#define B200KM_PATH_TC 2   /* tcgen05/TMEM/TMA fused pass (where the shape allows): the TF32 screen kernel with
+                              float64 re-decision for passes that need no per-row distance, else split-TF32 */
+#define B200KM_PATH_TC_SPLIT 3 /* tcgen05 path, split-TF32 kernel for every pass */
 
 /* init modes for b200km_init_centroids; reference: clustering.py:72 ("initMode" -> "init"),
  * values "random" and "k-means||" (clustering.py:185-186, tests/test_kmeans.py:84,93). */
@@ -89,6 +91,12 @@ int b200km_tc_supported(int d, int k, int with_update);
 int b200km_profile_enable(b200km_handle* h, int on);
 int b200km_profile_read(b200km_handle* h, double* kernel_ms_total, int* kernel_launches,
                         long long* all_launches);
+
+/* Diagnostics of the tcgen05 path (synchronises the device): refined_rows = rows the screen kernel re-decided
+ * in float64 since the last centroid preparation (one fit, or one lloyd_step / predict call); last_kernel =
+ * kernel of the last pass (0 FFMA kernels, 1 split-TF32 fused kernel, 2 screen kernel).  No counterpart in
+ * the reference. */
+int b200km_screen_stats(b200km_handle* h, long long* refined_rows, int* last_kernel);
 
 /* Bytes of library-owned device workspace a fit/predict of this shape needs. */
 int b200km_query_workspace(int64_t n, int d, int k, size_t* bytes_out);

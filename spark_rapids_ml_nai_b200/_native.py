@@ -12,7 +12,7 @@ from typing import Optional, Tuple
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "lib", "libb200km.so")
 
-PATH_AUTO, PATH_FFMA, PATH_TC = 0, 1, 2
+PATH_AUTO, PATH_FFMA, PATH_TC, PATH_TC_SPLIT = 0, 1, 2, 3
 INIT_RANDOM, INIT_KMEANS_PARALLEL = 0, 1
 UNIQUE_ID_BYTES = 128
 
@@ -31,6 +31,7 @@ _SIGNATURES = {
     "b200km_profile_enable": (_c.c_int, [_c.c_void_p, _c.c_int]),
     "b200km_profile_read": (_c.c_int, [_c.c_void_p, _c.POINTER(_c.c_double), _c.POINTER(_c.c_int),
                                        _c.POINTER(_c.c_longlong)]),
+    "b200km_screen_stats": (_c.c_int, [_c.c_void_p, _c.POINTER(_c.c_longlong), _c.POINTER(_c.c_int)]),
     "b200km_query_workspace": (_c.c_int, [_c.c_int64, _c.c_int, _c.c_int, _c.POINTER(_c.c_size_t)]),
     "b200km_fit": (_c.c_int, [_c.c_void_p, _c.c_void_p, _c.c_int64, _c.c_int, _c.c_int, _c.c_void_p, _c.c_int,
                               _c.c_double, _c.c_void_p, _c.POINTER(_c.c_double), _c.POINTER(_c.c_int),
@@ -188,6 +189,13 @@ class Handle:
                                  float(tol), out.data_ptr(), ctypes.byref(inertia) if want_inertia else None,
                                  ctypes.byref(n_iter), _ptr(labels), _stream_ptr(stream)))
         return out, (inertia.value if want_inertia else None), n_iter.value, labels
+
+    def screen_stats(self) -> Tuple[int, int]:
+        """(rows re-decided in float64 by the screen kernel since the last centroid preparation, kernel of the
+        last pass: 0 FFMA, 1 split-TF32, 2 screen)."""
+        r, kk = ctypes.c_longlong(0), ctypes.c_int(0)
+        _check(load().b200km_screen_stats(self._h, ctypes.byref(r), ctypes.byref(kk)))
+        return int(r.value), int(kk.value)
 
     def lloyd_step(self, X, centroids, want_labels: bool = False, stream=None):
         """One assign+accumulate pass: (sums f64 [k,d], counts f64 [k], inertia f64 [1], labels or None)."""

@@ -110,6 +110,8 @@ struct b200km_handle {
     unsigned int* d_work = nullptr;
     size_t n_cap = 0;
     TcWorkspace tc;
+    bool split_only = false;  // this fit saw too many float64 re-decisions in the screen kernel
+    int last_kernel = 0;      // 0 = FFMA kernels, 1 = split-TF32 fused kernel, 2 = screen kernel
     // instrumentation (b200km_profile_*)
     bool prof = false;
     static constexpr int kProfMax = 256;
@@ -194,30 +196,45 @@ int check_shape(const b200km_handle* h, const void* X, int64_t n, int d, int k) 
 // Picks the kernel path for this shape, honouring a forced path (and failing if it cannot run).
 int pick_path(b200km_handle* h, const float* X, int d, int k, bool with_acc, bool* use_tc) {
     const bool can = tc_supported(X, d, k, with_acc);
-    if (h->path == B200KM_PATH_TC && !can)
+    if ((h->path == B200KM_PATH_TC || h->path == B200KM_PATH_TC_SPLIT) && !can)
         return fail("tcgen05 path forced but not available for d=%d k=%d (needs d%%4==0, 16B-aligned X, "
                     "d<=%d, k<=%d and the split centroids%s to fit shared memory)", d, k, tc_max_d(), tc_max_k(),
                     with_acc ? " + float64 accumulators" : "");
-    *use_tc = (h->path == B200KM_PATH_TC) || (h->path == B200KM_PATH_AUTO && can);
+    const bool forced = h->path == B200KM_PATH_TC || h->path == B200KM_PATH_TC_SPLIT;
+    *use_tc = forced || (h->path == B200KM_PATH_AUTO && can);
     h->last_path = *use_tc ? "tc" : "ffma";
     return 0;
 }
 
 // One assignment (+ optional accumulation) pass on the chosen path.
-// labels/best may be workspace or caller buffers.  acc == nullptr -> assignment only.
+// labels / best: caller buffers, or nullptr when the caller does not need them (the FFMA kernels then use
+// the workspace arrays).  acc == nullptr -> assignment only.  On the tcgen05 path a pass that needs no
+// per-row distances runs the screen kernel, every other one the split-TF32 kernel.
 int run_pass(b200km_handle* h, bool use_tc, const float* X, int64_t n, int d, int k, const float* C,
              int32_t* labels, float* best, double* acc, bool honor_done, bool xn_compute, cudaStream_t s) {
     // the dominant kernel of the pass is bracketed by an event pair when profiling is on
     const bool rec = h->prof && h->prof_n < b200km_handle::kProfMax;
     if (rec) CU_TRY(cudaEventRecord(h->pev[2 * h->prof_n], s));
     if (use_tc) {
-        if (tc_pass(&h->tc, X, n, d, k, C, h->d_cnorm, h->d_xnorm, xn_compute, labels, best, acc, h->d_state, honor_done, s))
+        const bool screen = h->path != B200KM_PATH_TC_SPLIT && !h->split_only && best == nullptr &&
+                            screen_supported(X, d, k, acc != nullptr);
+        if (screen) {
+            if (screen_pass(&h->tc, X, n, d, k, C, h->d_cnorm, h->d_xnorm, (float*)h->d_work, xn_compute, labels, acc, h->d_state,
+                            honor_done, s))
+                return fail("tcgen05 screen pass failed: %s", screen_last_error());
+        } else if (tc_pass(&h->tc, X, n, d, k, C, h->d_cnorm, h->d_xnorm, xn_compute, labels, best, acc, h->d_state,
+                           honor_done, s)) {
             return fail("tcgen05 pass failed: %s", tc_last_error());
+        }
+        h->last_kernel = screen ? 2 : 1;
         if (rec) CU_TRY(cudaEventRecord(h->pev[2 * h->prof_n + 1], s));
         if (rec) h->prof_n++;
-        h->launches += 1;
+        h->launches += 2;  // operand preparation + the fused kernel
         return 0;
     }
+    if (!labels) labels = h->d_labels;
+    if (!best) best = h->d_best;
+    h->last_kernel = 0;
     launch_assign_ffma(X, n, d, C, k, h->d_cnorm, h->d_xnorm, labels, best, h->d_state, h->d_work, honor_done, s);
     if (rec) CU_TRY(cudaEventRecord(h->pev[2 * h->prof_n + 1], s));
     if (rec) h->prof_n++;
@@ -321,7 +338,7 @@ int b200km_abort(b200km_handle* h) {
 
 int b200km_set_path(b200km_handle* h, int path) {
     if (!h) return fail("null handle");
-    if (path < B200KM_PATH_AUTO || path > B200KM_PATH_TC) return fail("unknown path %d", path);
+    if (path < B200KM_PATH_AUTO || path > B200KM_PATH_TC_SPLIT) return fail("unknown path %d", path);
     h->path = path;
     return 0;
 }
@@ -362,13 +379,23 @@ int b200km_profile_read(b200km_handle* h, double* kernel_ms_total, int* kernel_l
     return 0;
 }
 
+int b200km_screen_stats(b200km_handle* h, long long* refined_rows, int* last_kernel) {
+    if (!h) return fail("null handle");
+    CU_TRY(cudaSetDevice(h->device));
+    IterState st;
+    CU_TRY(cudaMemcpy(&st, h->d_state, sizeof(st), cudaMemcpyDeviceToHost));
+    if (refined_rows) *refined_rows = (long long)st.screen_refined;
+    if (last_kernel) *last_kernel = h->last_kernel;
+    return 0;
+}
+
 int b200km_query_workspace(int64_t n, int d, int k, size_t* bytes_out) {
     if (!bytes_out) return fail("bytes_out is null");
     if (n < 0 || d <= 0 || k <= 0) return fail("bad shape");
     const size_t kd = (size_t)k * d;
     size_t b = sizeof(double) * (kd + k + 1 + 64) + sizeof(double) * (k + 64) + sizeof(float) * (k + 64) +
                sizeof(float) * (kd + kd / 8 + 64) + 16 * ((size_t)n + (size_t)n / 8 + 256) + sizeof(IterState);
-    b += tc_workspace_bytes(d, k);
+    b += tc_workspace_bytes(d, k) > screen_workspace_bytes(d, k) ? tc_workspace_bytes(d, k) : screen_workspace_bytes(d, k);
     *bytes_out = b;
     return 0;
 }
@@ -388,6 +415,7 @@ int b200km_fit(b200km_handle* h, const float* X, int64_t n_local, int d, int k, 
     const size_t kd = (size_t)k * d;
     const int64_t acc_len = (int64_t)kd + k + 1;
 
+    h->split_only = false;
     CU_TRY(cudaMemcpyAsync(h->d_C, init_centroids, sizeof(float) * kd, cudaMemcpyDeviceToDevice, s));
     if (!use_tc) launch_rownorm(X, n_local, d, h->d_xnorm, s);
     launch_prep(h->d_C, k, d, h->d_cnorm, h->d_acc, acc_len, h->d_state, true, s);
@@ -399,8 +427,13 @@ int b200km_fit(b200km_handle* h, const float* X, int64_t n_local, int d, int k, 
         if (it >= kRing) {
             CU_TRY(cudaEventSynchronize(h->ev[slot]));
             if (h->h_state[slot].done) break;
+            // The screen kernel pays a float64 look for every row inside its (wide) TF32 band.  When the
+            // passes seen so far re-decided more than 2% of their rows the data has no margin to screen
+            // with: the remaining passes run the split-TF32 kernel, whose band is ~200x narrower.
+            const double seen = (double)n_local * (double)(it - kRing + 1);
+            if (!h->split_only && (double)h->h_state[slot].screen_refined > 0.02 * seen) h->split_only = true;
         }
-        if (run_pass(h, use_tc, X, n_local, d, k, h->d_C, h->d_labels, h->d_best, h->d_acc, true, it == 0, s)) return 1;
+        if (run_pass(h, use_tc, X, n_local, d, k, h->d_C, nullptr, nullptr, h->d_acc, true, it == 0, s)) return 1;
         if (h->nranks > 1)
             NCCL_TRY(g_nccl.AllReduce(h->d_acc, h->d_acc, (size_t)acc_len, ncclFloat64, ncclSum, h->comm, s));
         launch_finalize(h->d_C, k, d, h->d_cnorm, h->d_acc, h->d_shift, tol, h->d_state, s);
@@ -444,8 +477,14 @@ int b200km_lloyd_step(b200km_handle* h, const float* X, int64_t n, int d, int k,
     if (!use_tc) launch_rownorm(X, n, d, h->d_xnorm, s);
     launch_prep(centroids, k, d, h->d_cnorm, h->d_acc, (int64_t)kd + k + 1, h->d_state, true, s);
     CU_TRY(cudaGetLastError());
-    int32_t* lab = labels_out ? labels_out : h->d_labels;
-    if (n > 0 && run_pass(h, use_tc, X, n, d, k, centroids, lab, h->d_best, h->d_acc, false, true, s)) return 1;
+    h->split_only = false;
+    if (n > 0) {
+        if (run_pass(h, use_tc, X, n, d, k, centroids, labels_out, nullptr, h->d_acc, false, true, s)) return 1;
+        if (h->last_kernel == 2) {
+            screen_inertia_fix(centroids, k, d, h->d_acc, s);
+            h->launches += 1;
+        }
+    }
     CU_TRY(cudaMemcpyAsync(sums_out, h->d_acc, sizeof(double) * kd, cudaMemcpyDeviceToDevice, s));
     CU_TRY(cudaMemcpyAsync(counts_out, h->d_acc + kd, sizeof(double) * k, cudaMemcpyDeviceToDevice, s));
     CU_TRY(cudaMemcpyAsync(inertia_out, h->d_acc + kd + k, sizeof(double), cudaMemcpyDeviceToDevice, s));
@@ -466,8 +505,8 @@ int b200km_predict(b200km_handle* h, const float* X, int64_t n, int d, const flo
     if (!use_tc) launch_rownorm(X, n, d, h->d_xnorm, s);
     launch_prep(centroids, k, d, h->d_cnorm, nullptr, 0, h->d_state, false, s);
     CU_TRY(cudaGetLastError());
-    float* best = min_dist_out ? min_dist_out : h->d_best;
-    return run_pass(h, use_tc, X, n, d, k, centroids, labels_out, best, nullptr, false, true, s);
+    h->split_only = false;
+    return run_pass(h, use_tc, X, n, d, k, centroids, labels_out, min_dist_out, nullptr, false, true, s);
 }
 
 int b200km_init_centroids(b200km_handle* h, const float* X, int64_t n_local, int d, int k, int mode,

@@ -13,7 +13,7 @@ struct IterState {
     unsigned int amb_count;  // entries in the near-tie work list of the current pass
     double shift2;       // sum_j ||c_new_j - c_old_j||^2 of the last executed iteration
     float cnorm_max;     // max_j ||c_j||^2 of the current centroids
-    int pad;
+    unsigned int screen_refined;  // rows the screen kernel re-decided in float64 since the last prep
 };
 
 // Near-tie band: a row whose best and second-best approximate scores differ by less than

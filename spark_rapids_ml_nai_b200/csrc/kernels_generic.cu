@@ -92,6 +92,7 @@ __global__ void __launch_bounds__(128) cnorm_kernel(const float* __restrict__ C,
         if (threadIdx.x == 0) {
             st->cnorm_max = fmaxf(fmaxf(red[0], red[1]), fmaxf(red[2], red[3]));
             st->amb_count = 0;
+            st->screen_refined = 0;
             if (reset_iter) {
                 st->done = 0;
                 st->n_iter = 0;

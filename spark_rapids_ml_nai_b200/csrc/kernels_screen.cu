@@ -1,0 +1,1078 @@
+// tcgen05 "screen" kernel: the Lloyd-iteration pass (and the labels-only predict pass).
+//
+// One persistent, warp-specialised kernel reads every 128-row tile of X once (TMA) and, while the tile sits
+// in shared memory,
+//   1. scores it against the centroids on the tensor cores straight from shared memory: A = the raw FP32
+//      tile (the tensor core reads the top 19 bits of each word, i.e. x truncated to TF32), B = the stacked
+//      TF32 split [c_hi ; c_lo] of the centroids, FP32 accumulation in TMEM; the assign warps form
+//      D_j = ||x||^2 + ||c_j||^2 - 2 x^.c_j;
+//   2. decides which rows the TF32 view of x cannot decide.  With x^ = trunc(x), ||x - x^|| <= 2^-10 ||x||,
+//      so the error of a MARGIN D_a - D_b is bounded by 2 * 2^-10 ||x|| * ||c_a - c_b|| (+ the FP32 rounding
+//      terms): it scales with the distance between the two centroids, not with their norms.  A centroid j
+//      can truly beat the computed best c_1 only if ||c_1 - c_j|| <= 2 r_1 (r_1 = distance to c_1), hence a
+//      row is safe when its runner-up margin exceeds the bound for the pair (table of pairwise centroid
+//      distances) and every other margin exceeds 4 * 2^-10 ||x|| r_1.  Any other row is re-decided exactly
+//      in float64 from the tile in shared memory - labels are exact for every row;
+//   3. sorts the tile's rows by label and adds them (exact FP32 data, not the TF32 view) into per-cluster
+//      sums held in registers / float64 shared memory.
+// Nothing but labels leaves the kernel per row.  The inertia of the pass follows exactly from the float64
+// sums:  sum_i ||x_i - c_l(i)||^2 = sum_i ||x_i||^2 - 2 sum_j c_j.S_j + sum_j n_j ||c_j||^2  (screen_inertia_fix).
+//
+// When too many rows need the float64 look (structureless data) b200km_fit switches to the split-TF32 kernel
+// (kernels_tc.cu), which also splits x and therefore needs no re-decision beyond FP32 rounding.
+//
+// Warp roles (704 threads, 1 CTA per SM, grid = #SMs):
+//   warp 0       TMA producer (centroids once, then X tiles: 32-float SWIZZLE_128B K-atoms + a narrow tail)
+//   warp 1       TMEM allocator + MMA issuer (warp-uniform loop, one elected lane, A and B via UMMA descriptors)
+//   warps 2-5    row norms ||x||^2 (first pass of a fit only; later passes read them back from HBM)
+//   warps 6-13   assign, two groups taking alternate tiles: tcgen05.ld, top-2, safety test, float64
+//                re-decision, counting sort by label
+//   warps 14-21  update: label-sorted accumulation; warp = label range, lane = float4 column chunk
+//
+// Replaces cuML's fusedL2NN + reduce_rows_by_key pair behind reference
+// python/src/spark_rapids_ml/clustering.py:367-370 (fit) and :493-497 (predict).
+#include "tc.cuh"
+#include "tc_ptx.cuh"
+
+#include <cfloat>
+#include <climits>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+
+namespace b200km {
+
+namespace {
+
+using namespace tcx;
+
+thread_local char g_sc_err[512] = "";
+
+constexpr int kTileM = 128;
+constexpr int kAtomBytes = kTileM * 128;  // one full K-atom of an X tile: 128 rows x 32 floats
+constexpr int kThreads = 704;
+constexpr int kNormWarp0 = 2, kAssignWarp0 = 6, kUpdateWarp0 = 14;
+constexpr int kMaxSmem = 227 * 1024;
+constexpr int kMaxStages = 4;
+constexpr int kMaxND = 4;
+constexpr int kMaxD = 256;
+constexpr int kMaxK = 256;
+constexpr int kHist = kMaxK + 8;
+
+struct ScParams {
+    int64_t n;
+    int64_t num_tiles;
+    int d, k, k_pad;
+    int n_full;     // number of 32-float SWIZZLE_128B atoms
+    int tail_cols;  // 0, 8 (SWIZZLE_32B) or 16 (SWIZZLE_64B): width of the narrow last atom
+    int num_stages, num_d;
+    int stage_bytes;
+    const float* C;
+    const float* cnorm;
+    float* xnorm;  // [n] ||x||^2: written when xn_compute, read otherwise
+    float* xlo;    // [n] ||x - trunc_tf32(x)||^2: likewise
+    int xn_compute;
+    int32_t* labels;  // may be null
+    double* acc;      // [k*d | k | 1] or null (labels-only pass)
+    IterState* st;
+    int honor_done;
+    const float* pd;  // [k][k] upper bounds of ||c_a - c_b||
+    float tol_x;      // slack on the FP32 value of ||x - trunc_tf32(x)||
+    float eps_rel;    // FP32 rounding terms of a margin, relative to ||x||^2 + max ||c||^2
+    float abs_rel;    // bound of the error of one D_j, relative to ||x||^2 + max ||c||^2
+    unsigned long long* trace;  // development aid (B200KM_TRACE)
+    int off_c, off_acc, off_cn, off_xn, off_pd, off_bar;
+};
+
+// D[tmem] (+)= A[smem desc] * B[smem desc], kind::tf32, M=128
+__device__ __forceinline__ void mma_tf32_ss(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc,
+                                            uint32_t accumulate) {
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t"
+        "}" ::"r"(d_tmem),
+        "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+
+// acc (two packed floats) += v when pos < end.  One FADD2 for two columns; the predicate lives inside the
+// asm so the row loop stays branch-free.
+__device__ __forceinline__ void add2_if(unsigned long long& acc, unsigned long long v, int pos, int end) {
+    asm("{\n\t"
+        ".reg .pred p;\n\t"
+        "setp.lt.s32 p, %2, %3;\n\t"
+        "@p add.rn.f32x2 %0, %0, %1;\n\t"
+        "}"
+        : "+l"(acc)
+        : "l"(v), "r"(pos), "r"(end));
+}
+__device__ __forceinline__ float2 unpack2(unsigned long long v) {
+    float2 r;
+    asm("mov.b64 {%0, %1}, %2;" : "=f"(r.x), "=f"(r.y) : "l"(v));
+    return r;
+}
+
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&r)[32]) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x32.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+        "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+          "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]),
+          "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]),
+          "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+        : "r"(taddr)
+        : "memory");
+}
+
+// Byte offset of 16-byte chunk `chunk` (= float column / 4) of row r inside one tile stage.  Full atoms
+// use the TMA 128-byte swizzle (chunk ^= row & 7); the narrow tail atom the 64-byte (chunk ^= (row>>1)&3)
+// or 32-byte (chunk ^= (row>>2)&1) swizzle.
+__device__ __forceinline__ uint32_t chunk_off(const ScParams& p, int r, int chunk) {
+    const int a = chunk >> 3;
+    if (a < p.n_full) return (uint32_t)(a * kAtomBytes + r * 128 + (((chunk & 7) ^ (r & 7)) << 4));
+    const int c = chunk - p.n_full * 8;
+    const uint32_t base = (uint32_t)(p.n_full * kAtomBytes);
+    if (p.tail_cols == 16) return base + (uint32_t)(r * 64 + ((c ^ ((r >> 1) & 3)) << 4));
+    return base + (uint32_t)(r * 32 + ((c ^ ((r >> 2) & 1)) << 4));
+}
+
+__device__ __forceinline__ void trace_ev(const ScParams& p, int64_t it, int ev) {
+#ifdef B200KM_ENABLE_TRACE
+    if (p.trace && blockIdx.x == 0 && it < 256) p.trace[it * 16 + ev] = (unsigned long long)clock64();
+#endif
+}
+
+// ------------------------------------------------------------------------------------------------
+// pd[a][b] = an upper bound of ||c_a - c_b|| (FP32 sum inflated by its own rounding bound)
+__global__ void __launch_bounds__(128) pairdist_kernel(const float* __restrict__ C, int k, int d,
+                                                       float* __restrict__ pd) {
+    const int pair = blockIdx.x * 4 + (threadIdx.x >> 5);
+    if (pair >= k * k) return;
+    const int a = pair / k, b = pair - a * k;
+    const int lane = threadIdx.x & 31;
+    float s = 0.f;
+    for (int i = lane; i < d; i += 32) {
+        const float df = C[(size_t)a * d + i] - C[(size_t)b * d + i];
+        s = fmaf(df, df, s);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+    if (lane == 0) pd[pair] = sqrtf(s) * (1.f + 1e-5f) + 1e-30f;
+}
+
+// acc[k*d + k] (which holds sum_i ||x_i||^2 after the screen kernel) += sum_j (n_j ||c_j||^2 - 2 c_j.S_j),
+// all in float64 from the pass's own sums: the exact inertia of the pass's labels against `C`.
+__global__ void __launch_bounds__(256) screen_inertia_fix_kernel(const float* __restrict__ C, int k, int d,
+                                                                 double* __restrict__ acc) {
+    __shared__ double red[8];
+    double t = 0.0;
+    const size_t kd = (size_t)k * d;
+    for (size_t idx = threadIdx.x; idx < kd; idx += blockDim.x) {
+        const double c = (double)C[idx];
+        const double cnt = acc[kd + idx / d];
+        t += c * (cnt * c - 2.0 * acc[idx]);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) t += __shfl_xor_sync(0xffffffffu, t, o);
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = t;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double s = 0.0;
+        for (int w = 0; w < 8; ++w) s += red[w];
+        const double v = acc[kd + k] + s;
+        acc[kd + k] = v > 0.0 ? v : 0.0;
+    }
+}
+
+// ||x||^2 and ||x - trunc_tf32(x)||^2 of one row of the tile in `stage` (interleaved partial sums)
+__device__ __forceinline__ void acc_norms(const float4 v, float (&s)[4], float (&l)[4]) {
+    const float e[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+    for (int t = 0; t < 4; ++t) {
+        s[t] = fmaf(e[t], e[t], s[t]);
+        const float r = e[t] - __uint_as_float(tf32_trunc(__float_as_uint(e[t])));  // exact
+        l[t] = fmaf(r, r, l[t]);
+    }
+}
+__device__ __forceinline__ float2 row_norms(const ScParams& p, const uint8_t* stage, int row) {
+    float s[4] = {0.f, 0.f, 0.f, 0.f}, l[4] = {0.f, 0.f, 0.f, 0.f};
+    for (int a = 0; a < p.n_full; ++a) {
+        const uint8_t* rowp = stage + a * kAtomBytes + row * 128;
+#pragma unroll
+        for (int c = 0; c < 8; ++c) acc_norms(*reinterpret_cast<const float4*>(rowp + ((c ^ (row & 7)) << 4)), s, l);
+    }
+    if (p.tail_cols) {
+        const int nch = p.tail_cols >> 2;
+        for (int c = 0; c < nch; ++c)
+            acc_norms(*reinterpret_cast<const float4*>(stage + chunk_off(p, row, p.n_full * 8 + c)), s, l);
+    }
+    return make_float2((s[0] + s[1]) + (s[2] + s[3]), (l[0] + l[1]) + (l[2] + l[3]));
+}
+
+__global__ void __launch_bounds__(kThreads, 1)
+    kmeans_screen_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ CUtensorMap tmXt,
+                         const __grid_constant__ CUtensorMap tmC, const __grid_constant__ CUtensorMap tmCt,
+                         const ScParams p) {
+    if (p.honor_done && p.st->done) return;
+
+    extern __shared__ uint8_t smem_raw[];
+    __shared__ uint8_t s_hist[2][2][4][kHist];         // per assign group, double-buffered by tile: per-warp label counts
+    __shared__ unsigned short s_off[2][4][kHist];      // per assign group: per-warp start offsets (only when k >= 32)
+    __shared__ unsigned short s_cand[2][kTileM][4];    // per assign group: candidate centroids of near-tie rows
+    __shared__ unsigned short s_base[2][kHist];        // start of every label's run in the sorted order (double-buffered)
+    __shared__ int s_perm[2][kTileM + 8];   // sorted position -> low 16 bits: row offset in a full atom
+                                            // (r*128 | swizzle); bit 16: first row of its run; bits 17+: label
+    __shared__ int s_permT[2][kTileM + 8];  // same for the narrow tail atom (row pitch 64 / 32 bytes)
+    uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
+    const uint32_t smem_base = smem_u32(smem);
+
+    const int warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
+    const int S = p.num_stages;
+    const int ND = p.num_d;  // power of two
+    const int stage_bytes = p.stage_bytes;
+    const int c_block = 2 * p.k_pad * 128;  // bytes of one full-atom block [c_hi rows | c_lo rows]
+    const bool stacked = p.k_pad <= 128;
+    const int dcols = stacked ? 2 * p.k_pad : p.k_pad;
+
+    // barrier table
+    const uint32_t bar0 = smem_base + p.off_bar;
+    const uint32_t x_full0 = bar0, x_empty0 = bar0 + 32, xn_full0 = bar0 + 64, d_full0 = bar0 + 96,
+                   d_empty0 = bar0 + 128, s_full0 = bar0 + 160, s_empty0 = bar0 + 176, c_full = bar0 + 192;
+    uint32_t* tmem_slot = (uint32_t*)(smem + p.off_bar + 200);
+
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < kMaxStages; ++s) {
+            mbar_init(x_full0 + 8u * s, 1);
+            mbar_init(x_empty0 + 8u * s, p.acc ? 8 : 4);
+            mbar_init(xn_full0 + 8u * s, 4);
+        }
+        for (int s = 0; s < kMaxND; ++s) {
+            mbar_init(d_full0 + 8u * s, 1);
+            mbar_init(d_empty0 + 8u * s, 4);
+        }
+        for (int s = 0; s < 2; ++s) {
+            mbar_init(s_full0 + 8u * s, 4);
+            mbar_init(s_empty0 + 8u * s, 8);
+        }
+        mbar_init(c_full, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 1) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)),
+                     "r"(512));
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::);
+    }
+    {
+        // shared state every role relies on, written once by all threads before the first barrier
+        float* cn_init = (float*)(smem + p.off_cn);
+#pragma unroll 1
+        for (int j = threadIdx.x; j < p.k_pad; j += kThreads) cn_init[j] = (j < p.k) ? p.cnorm[j] : FLT_MAX;
+        if (p.k <= 32) {
+            float* pd_init = (float*)(smem + p.off_pd);
+#pragma unroll 1
+            for (int i = threadIdx.x; i < 32 * 32; i += kThreads) {
+                const int a = i >> 5, b = i & 31;
+                pd_init[i] = (a < p.k && b < p.k) ? p.pd[a * p.k + b] : 0.f;
+            }
+        }
+        if (p.acc) {
+            double* sacc_init = (double*)(smem + p.off_acc);
+#pragma unroll 1
+            for (int i = threadIdx.x; i < p.k * p.d + p.k; i += kThreads) sacc_init[i] = 0.0;
+        }
+#pragma unroll 1
+        for (int i = threadIdx.x; i < 2 * 2 * 4 * kHist; i += kThreads) (&s_hist[0][0][0][0])[i] = 0;
+#pragma unroll 1
+        for (int i = threadIdx.x; i < 2 * (kTileM + 8); i += kThreads) {
+            (&s_perm[0][0])[i] = 0;
+            (&s_permT[0][0])[i] = 0;
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    const int64_t first_tile = blockIdx.x;
+    const int64_t tile_step = gridDim.x;
+
+    if (warp == 0) {
+        // ===================================== TMA producer =====================================
+        if (lane == 0) {
+            mbar_arrive_expect_tx(c_full, (uint32_t)(2 * p.k_pad * (p.n_full * 128 + p.tail_cols * 4)));
+            for (int a = 0; a < p.n_full; ++a)
+                for (int part = 0; part < 2; ++part)  // atom block = [c_hi rows | c_lo rows], 2*k_pad rows
+                    tma_load_2d(smem_base + p.off_c + a * c_block + part * p.k_pad * 128, &tmC, c_full, a * 32,
+                                part * p.k_pad);
+            if (p.tail_cols)
+                for (int part = 0; part < 2; ++part)
+                    tma_load_2d(smem_base + p.off_c + p.n_full * c_block + part * p.k_pad * p.tail_cols * 4, &tmCt,
+                                c_full, p.n_full * 32, part * p.k_pad);
+            int64_t it = 0;
+            for (int64_t tile = first_tile; tile < p.num_tiles; tile += tile_step, ++it) {
+                const int s = (int)(it % S);
+                mbar_wait(x_empty0 + 8u * s, (uint32_t)(((it / S) & 1) ^ 1));
+                trace_ev(p, it, 0);
+                mbar_arrive_expect_tx(x_full0 + 8u * s, (uint32_t)stage_bytes);
+                const uint32_t dst = smem_base + s * stage_bytes;
+                for (int a = 0; a < p.n_full; ++a)
+                    tma_load_2d(dst + a * kAtomBytes, &tmX, x_full0 + 8u * s, a * 32, (int)(tile * kTileM));
+                if (p.tail_cols)
+                    tma_load_2d(dst + p.n_full * kAtomBytes, &tmXt, x_full0 + 8u * s, p.n_full * 32,
+                                (int)(tile * kTileM));
+            }
+        }
+        __syncwarp();
+    } else if (warp == 1) {
+        // ====================================== MMA issuer ======================================
+        // The whole warp runs the loop and one elected lane issues (a tcgen05.mma issued from divergent
+        // code costs ~100 cycles per instruction, ~40 from warp-uniform code: tools/mma_bench.cu).  Both
+        // operands come from shared memory: A = the X tile exactly as TMA wrote it (K-major, swizzled), B =
+        // the TF32 centroids; consecutive K-steps differ only in the descriptors' start address (+32 B).
+        // k_pad <= 128: B is the stacked block [c_hi ; c_lo] (N = 2*k_pad, one instruction per K-step; the
+        // assign warps add the two halves); larger k: two instructions per K-step into the same columns.
+        const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(kTileM >> 4) << 24) |
+                               ((uint32_t)(dcols >> 3) << 17);
+        const int tail_row_bytes = p.tail_cols ? p.tail_cols * 4 : 128;
+        const uint64_t bdesc_full = make_b_desc(smem_base + p.off_c, 128);
+        const uint64_t bdesc_tail = make_b_desc(smem_base + p.off_c + p.n_full * c_block, tail_row_bytes);
+        const uint64_t adesc_full = make_b_desc(smem_base, 128);
+        const uint64_t adesc_tail = make_b_desc(smem_base + p.n_full * kAtomBytes, tail_row_bytes);
+        const uint64_t lo_full = (uint64_t)((p.k_pad * 128) >> 4);             // c_lo rows inside an atom block
+        const uint64_t lo_tail = (uint64_t)((p.k_pad * tail_row_bytes) >> 4);
+        const int tail_steps = p.tail_cols >> 3;
+        mbar_wait(c_full, 0);
+        int64_t it = 0;
+        for (int64_t tile = first_tile; tile < p.num_tiles; tile += tile_step, ++it) {
+            const int s = (int)(it % S);
+            const int db = (int)(it & (ND - 1));
+            mbar_wait(d_empty0 + 8u * db, (uint32_t)(((it / ND) & 1) ^ 1));
+            mbar_wait(x_full0 + 8u * s, (uint32_t)((it / S) & 1));
+            tc_fence_after();
+            if (lane == 0) trace_ev(p, it, 1);
+            const uint32_t d_tmem = tmem_base + (uint32_t)(db * dcols);
+            const uint64_t soff = (uint64_t)((s * stage_bytes) >> 4);
+            if (elect_one()) {
+                uint64_t ad = adesc_full + soff, bd = bdesc_full;
+#pragma unroll 1
+                for (int a = 0; a < p.n_full; ++a) {
+#pragma unroll
+                    for (int kk = 0; kk < 4; ++kk) {
+                        mma_tf32_ss(d_tmem, ad + 2 * kk, bd + 2 * kk, idesc, (a | kk) != 0);
+                        if (!stacked) mma_tf32_ss(d_tmem, ad + 2 * kk, bd + lo_full + 2 * kk, idesc, 1);
+                    }
+                    ad += (uint64_t)(kAtomBytes >> 4);
+                    bd += (uint64_t)(c_block >> 4);
+                }
+#pragma unroll 1
+                for (int kk = 0; kk < tail_steps; ++kk) {
+                    mma_tf32_ss(d_tmem, adesc_tail + soff + 2 * kk, bdesc_tail + 2 * kk, idesc, (p.n_full | kk) != 0);
+                    if (!stacked) mma_tf32_ss(d_tmem, adesc_tail + soff + 2 * kk, bdesc_tail + lo_tail + 2 * kk, idesc, 1);
+                }
+                tc_commit(d_full0 + 8u * db);
+                trace_ev(p, it, 2);
+            }
+            __syncwarp();
+        }
+    } else if (warp >= kNormWarp0 && warp < kAssignWarp0) {
+        // ======================================= row norms ======================================
+        if (p.xn_compute) {
+            const int row = (warp - kNormWarp0) * 32 + lane;
+            float* xn_s = (float*)(smem + p.off_xn);
+            int64_t it = 0;
+            for (int64_t tile = first_tile; tile < p.num_tiles; tile += tile_step, ++it) {
+                const int s = (int)(it % S);
+                mbar_wait(x_full0 + 8u * s, (uint32_t)((it / S) & 1));
+                const float2 nn = row_norms(p, smem + (size_t)s * stage_bytes, row);
+                const int64_t grow = tile * kTileM + row;
+                if (grow < p.n) {
+                    p.xnorm[grow] = nn.x;
+                    p.xlo[grow] = nn.y;
+                }
+                xn_s[s * kTileM + row] = nn.x;
+                xn_s[(kMaxStages + s) * kTileM + row] = nn.y;
+                __syncwarp();
+                if (lane == 0) mbar_arrive(xn_full0 + 8u * s);
+            }
+        }
+    } else if (warp >= kAssignWarp0 && warp < kUpdateWarp0) {
+        // ======================================== assign ========================================
+        // Two groups of four warps take alternate tiles (group g owns the sort buffer of its parity), so the
+        // argmin / re-decision / sort latency of one tile overlaps the next tile's.
+        const int g = (warp - kAssignWarp0) >> 2;
+        const int q = warp & 3;  // = the warp's TMEM lane quarter
+        const int row = q * 32 + lane;
+        const int et = threadIdx.x - (kAssignWarp0 + 4 * g) * 32;  // 0..127 within the group
+        const int bar_id = 1 + g;
+        float* cn_s = (float*)(smem + p.off_cn);
+        float* xn_s = (float*)(smem + p.off_xn);
+        const float cmax = p.st->cnorm_max;
+        const float* pd_s = (const float*)(smem + p.off_pd);
+        const bool fast = stacked && p.k_pad <= 32;
+        const int sb = g;
+
+        double sum_xn = 0.0;
+        unsigned int n_refined = 0;
+        for (int64_t it = g;; it += 2) {
+            const int64_t tile = first_tile + it * tile_step;
+            if (tile >= p.num_tiles) break;
+            const int s = (int)(it % S);
+            const int db = (int)(it & (ND - 1));
+            const int64_t grow = tile * kTileM + row;
+            const bool valid = grow < p.n;
+            float xn = 0.f, xl = 0.f;
+            if (!p.xn_compute && valid) {  // issued early, consumed after the scores
+                xn = p.xnorm[grow];
+                xl = p.xlo[grow];
+            }
+            mbar_wait(d_full0 + 8u * db, (uint32_t)((it / ND) & 1));
+            tc_fence_after();
+            if (et == 0) trace_ev(p, it, 4);
+
+            const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(db * dcols);
+            const uint8_t* stage = smem + (size_t)s * stage_bytes;
+            int label = 0;
+            unsigned m = 0;   // lanes whose row needs the float64 look
+            int ncand = 0;    // candidates of this lane's row (listed in s_cand when <= 4)
+            if (fast) {
+                // ---- k_pad <= 32: all scores stay in registers ----
+                uint32_t hi[32], lo[32];
+                tmem_ld32(taddr, hi);
+                tmem_ld32(taddr + 32, lo);
+                tmem_wait_ld();
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(d_empty0 + 8u * db);  // the score buffer is free again
+                mbar_wait(x_full0 + 8u * s, (uint32_t)((it / S) & 1));  // TMA writes visible to this thread
+                if (p.xn_compute) {
+                    mbar_wait(xn_full0 + 8u * s, (uint32_t)((it / S) & 1));
+                    xn = xn_s[s * kTileM + row];
+                    xl = xn_s[(kMaxStages + s) * kTileM + row];
+                }
+                // keys: D_j = ||x||^2 + ||c_j||^2 - 2 x^.c_j with the centroid index in the 5 low mantissa bits
+                // (a perturbation below 2^-18 |D_j|, covered by the bound)
+                float key[32];
+                const float4* cn4 = reinterpret_cast<const float4*>(cn_s);
+#pragma unroll
+                for (int j4 = 0; j4 < 8; ++j4) {
+                    const float4 c = cn4[j4];
+                    const float cc[4] = {c.x, c.y, c.z, c.w};
+#pragma unroll
+                    for (int t = 0; t < 4; ++t) {
+                        const int j = j4 * 4 + t;
+                        const float dot = __uint_as_float(hi[j]) + __uint_as_float(lo[j]);
+                        const float dj = fmaf(-2.f, dot, cc[t] + xn);  // padded columns: FLT_MAX
+                        key[j] = __uint_as_float((__float_as_uint(dj) & ~31u) | (uint32_t)j);
+                    }
+                }
+                // top-2 by a tournament of sorted pairs (independent operations, short dependency chains)
+                float m1[16], m2[16];
+#pragma unroll
+                for (int i = 0; i < 16; ++i) {
+                    m1[i] = fminf(key[2 * i], key[2 * i + 1]);
+                    m2[i] = fmaxf(key[2 * i], key[2 * i + 1]);
+                }
+#pragma unroll
+                for (int nn = 16; nn > 1; nn >>= 1) {
+#pragma unroll
+                    for (int i = 0; i < nn / 2; ++i) {
+                        const float a1 = m1[2 * i], a2 = m2[2 * i], b1 = m1[2 * i + 1], b2 = m2[2 * i + 1];
+                        m1[i] = fminf(a1, b1);
+                        m2[i] = fminf(fmaxf(a1, b1), fminf(a2, b2));
+                    }
+                }
+                const float b1 = m1[0], b2 = m2[0];
+                const int i1 = (int)(__float_as_uint(b1) & 31u), i2 = (int)(__float_as_uint(b2) & 31u);
+                label = i1;
+                // safety test (see the file header); every quantity is an upper bound
+                const float scale = xn + cmax;
+                const float t = p.tol_x * sqrtf(xl);  // >= ||x - x^||
+                const float eps = p.eps_rel * scale + 7.63e-6f * (fabsf(b1) + fabsf(b2));
+                const float r1 = sqrtf(fmaxf(b1, 0.f) + p.abs_rel * scale);
+                const float safe = 4.f * t * r1 + eps;
+                const float margin = b2 - b1;
+                const bool flag0 = valid && p.k > 1 && margin < safe;
+                bool amb = false;
+                if (__any_sync(0xffffffffu, flag0)) {
+                    const float thr = b1 + safe;
+                    int close = 0;
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) close += key[j] < thr ? 1 : 0;
+                    const bool pair_ok = margin >= 2.f * t * pd_s[i1 * 32 + i2] + eps;
+                    amb = flag0 && !(close == 2 && pair_ok);
+                    m = __ballot_sync(0xffffffffu, amb);
+                    if (m) {
+#pragma unroll
+                        for (int j = 0; j < 32; ++j) {
+                            if (amb && key[j] < thr) {
+                                if (ncand < 4) s_cand[g][row][ncand] = (unsigned short)j;
+                                ++ncand;
+                            }
+                        }
+                    }
+                }
+            } else {
+                // ---- general k: 16 scores at a time, running (best, second, argmin), loose bound ----
+                float b1 = FLT_MAX, b2 = FLT_MAX;
+                int i1 = 0;
+                for (int c0 = 0; c0 < p.k; c0 += 16) {
+                    uint32_t r[16], r2[16];
+                    tmem_ld16(taddr + c0, r);
+                    if (stacked) tmem_ld16(taddr + p.k_pad + c0, r2);
+                    tmem_wait_ld();
+#pragma unroll
+                    for (int j = 0; j < 16; ++j) {
+                        float dot = __uint_as_float(r[j]);
+                        if (stacked) dot += __uint_as_float(r2[j]);
+                        const float sc = fmaf(-2.f, dot, cn_s[c0 + j]);  // padded columns: FLT_MAX
+                        if (sc < b1) {
+                            b2 = b1;
+                            b1 = sc;
+                            i1 = c0 + j;
+                        } else {
+                            b2 = fminf(b2, sc);
+                        }
+                    }
+                }
+                mbar_wait(x_full0 + 8u * s, (uint32_t)((it / S) & 1));  // TMA writes visible to this thread
+                if (p.xn_compute) {
+                    mbar_wait(xn_full0 + 8u * s, (uint32_t)((it / S) & 1));
+                    xn = xn_s[s * kTileM + row];
+                }
+                label = i1;
+                // 2|x||c| <= |x|^2 + |c|^2: the pair bound with ||c_a - c_b|| <= 2 max||c||
+                const float band = (2.f * p.abs_rel + p.eps_rel) * (xn + cmax);
+                const bool amb = valid && p.k > 1 && (b2 - b1) < band;
+                m = __ballot_sync(0xffffffffu, amb);
+                // near-tie rows: a second look at the scores lists the candidates inside the band (first 4 kept)
+                if (m) {
+#pragma unroll 1
+                    for (int c0 = 0; c0 < p.k; c0 += 16) {
+                        uint32_t r[16], r2[16];
+                        tmem_ld16(taddr + c0, r);
+                        if (stacked) tmem_ld16(taddr + p.k_pad + c0, r2);
+                        tmem_wait_ld();
+#pragma unroll
+                        for (int j = 0; j < 16; ++j) {
+                            float dot = __uint_as_float(r[j]);
+                            if (stacked) dot += __uint_as_float(r2[j]);
+                            const float sc = fmaf(-2.f, dot, cn_s[c0 + j]);
+                            if (amb && (c0 + j) < p.k && (sc - b1) < band) {
+                                if (ncand < 4) s_cand[g][row][ncand] = (unsigned short)(c0 + j);
+                                ++ncand;
+                            }
+                        }
+                    }
+                }
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(d_empty0 + 8u * db);
+            }
+
+            // ---- exact re-decision, warp-cooperative: lane = float4 column chunk of the row.  FP32 squared
+            // differences first (no cancellation: their error is ~2^-21 of the distance itself); a margin
+            // inside that error is settled in float64. ----
+            while (m) {
+                const int src = __ffs(m) - 1;
+                m &= m - 1;
+                const int rr = q * 32 + src;
+                const int nc = __shfl_sync(0xffffffffu, ncand, src);
+                const int total = nc <= 4 ? nc : p.k;  // more than 4 candidates: scan every centroid
+                const int nchunks = p.d >> 2;
+                float f1 = FLT_MAX, f2 = FLT_MAX;
+                int bi = 0;
+                for (int t = 0; t < total; ++t) {
+                    const int j = nc <= 4 ? (int)s_cand[g][rr][t] : t;
+                    const float4* c4 = reinterpret_cast<const float4*>(p.C + (size_t)j * p.d);
+                    float sum = 0.f;
+                    for (int ch = lane; ch < nchunks; ch += 32) {
+                        const float4 xv = *reinterpret_cast<const float4*>(stage + chunk_off(p, rr, ch));
+                        const float4 cv = __ldg(c4 + ch);
+                        const float d0 = xv.x - cv.x, d1 = xv.y - cv.y, d2 = xv.z - cv.z, d3 = xv.w - cv.w;
+                        sum += fmaf(d0, d0, d1 * d1) + fmaf(d2, d2, d3 * d3);
+                    }
+#pragma unroll
+                    for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+                    if (sum < f1) {  // candidates come in ascending index order: ties keep the lowest
+                        f2 = f1;
+                        f1 = sum;
+                        bi = j;
+                    } else {
+                        f2 = fminf(f2, sum);
+                    }
+                }
+                if (total > 1 && (f2 - f1) <= 4e-6f * (f1 + f2)) {
+                    // float64 (rare)
+                    double bd = DBL_MAX;
+                    for (int t = 0; t < total; ++t) {
+                        const int j = nc <= 4 ? (int)s_cand[g][rr][t] : t;
+                        const float* c = p.C + (size_t)j * p.d;
+                        double sum = 0.0;
+                        for (int i = lane; i < p.d; i += 32) {
+                            const float xv = *reinterpret_cast<const float*>(stage + chunk_off(p, rr, i >> 2) + ((i & 3) << 2));
+                            const double df = (double)xv - (double)__ldg(c + i);
+                            sum = fma(df, df, sum);
+                        }
+#pragma unroll
+                        for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+                        if (sum < bd) {
+                            bd = sum;
+                            bi = j;
+                        }
+                    }
+                }
+                if (lane == src) {
+                    label = bi;
+                    ++n_refined;
+                }
+            }
+            if (valid) {
+                if (p.labels) p.labels[grow] = label;
+                sum_xn += (double)xn;
+            }
+            if (et == 0) trace_ev(p, it, 5);
+
+            if (p.acc) {
+                // ---- stable counting sort of the tile's rows by label (bin k = rows past the end) ----
+                // One barrier: every warp publishes its label counts, then each warp derives its own start
+                // offsets from all four count rows by itself (a scan over the bins), so there is no serial
+                // section.  The count rows are double-buffered by tile; a warp clears its row of the other
+                // buffer after the barrier (everyone is then done reading that buffer's previous use).
+                mbar_wait(s_empty0 + 8u * sb, (uint32_t)(((it >> 1) & 1) ^ 1));
+                const int hb = (int)((it >> 1) & 1);
+                uint8_t (*hist)[kHist] = s_hist[g][hb];
+                const int bins = p.k + 1;
+                const int bin = valid ? label : p.k;
+                const unsigned peers = __match_any_sync(0xffffffffu, bin);
+                const int rank_w = __popc(peers & ((1u << lane) - 1u));
+                if (rank_w == 0) hist[q][bin] = (uint8_t)__popc(peers);
+                named_bar_sync(bar_id, 128);
+                int pos, first;
+                if (bins <= 32) {
+                    // lane = bin
+                    const int h0 = hist[0][lane], h1 = hist[1][lane], h2 = hist[2][lane], h3 = hist[3][lane];
+                    const int tot = (lane < bins) ? h0 + h1 + h2 + h3 : 0;
+                    int incl = tot;
+#pragma unroll
+                    for (int o = 1; o < 32; o <<= 1) {
+                        const int v = __shfl_up_sync(0xffffffffu, incl, o);
+                        if (lane >= o) incl += v;
+                    }
+                    const int excl = incl - tot;
+                    const int mine = excl + (q > 0 ? h0 : 0) + (q > 1 ? h1 : 0) + (q > 2 ? h2 : 0);
+                    if (q == 0) s_base[sb][lane] = (unsigned short)excl;  // lanes >= bins hold the total (128)
+                    if (q == 0 && lane == 31) s_base[sb][32] = (unsigned short)incl;
+                    pos = __shfl_sync(0xffffffffu, mine, bin) + rank_w;
+                    first = pos == __shfl_sync(0xffffffffu, excl, bin);
+                } else {
+                    // lane owns `per` consecutive bins
+                    const int per = (bins + 31) >> 5;
+                    const int b0 = lane * per;
+                    int lane_total = 0;
+                    for (int bb = b0; bb < b0 + per && bb < bins; ++bb)
+                        lane_total += hist[0][bb] + hist[1][bb] + hist[2][bb] + hist[3][bb];
+                    int incl = lane_total;
+#pragma unroll
+                    for (int o = 1; o < 32; o <<= 1) {
+                        const int v = __shfl_up_sync(0xffffffffu, incl, o);
+                        if (lane >= o) incl += v;
+                    }
+                    int run = incl - lane_total;
+                    for (int bb = b0; bb < b0 + per && bb < bins; ++bb) {
+                        const int h0 = hist[0][bb], h1 = hist[1][bb], h2 = hist[2][bb], h3 = hist[3][bb];
+                        if (q == 0) s_base[sb][bb] = (unsigned short)run;
+                        s_off[g][q][bb] = (unsigned short)(run + (q > 0 ? h0 : 0) + (q > 1 ? h1 : 0) + (q > 2 ? h2 : 0));
+                        run += h0 + h1 + h2 + h3;
+                    }
+                    if (q == 0 && lane == 31) s_base[sb][bins] = (unsigned short)run;
+                    __syncwarp();
+                    const int start = s_off[g][q][bin];
+                    pos = start + rank_w;
+                    first = rank_w == 0 && hist[0][bin] * (q > 0) + hist[1][bin] * (q > 1) + hist[2][bin] * (q > 2) == 0;
+                }
+                {
+                    // sorted position -> row offset inside an atom (r*pitch | swizzle bits), a first-of-run flag
+                    // (bit 16) and the label (bits 17+)
+                    const int meta = (first ? (1 << 16) : 0) | (bin << 17);
+                    s_perm[sb][pos] = (row << 7) | ((row & 7) << 4) | meta;
+                    if (p.tail_cols == 16) s_permT[sb][pos] = (row << 6) | (((row >> 1) & 3) << 4) | meta;
+                    else if (p.tail_cols == 8) s_permT[sb][pos] = (row << 5) | (((row >> 2) & 1) << 4) | meta;
+                }
+                {
+                    uint8_t* nxt = s_hist[g][hb ^ 1][q];
+                    for (int bb = lane; bb < bins; bb += 32) nxt[bb] = 0;  // own row of the other buffer
+                }
+                __syncwarp();  // the warp's s_perm writes precede its arrival; the update group waits for all four
+                if (et == 0) trace_ev(p, it, 6);
+                if (lane == 0) mbar_arrive(s_full0 + 8u * sb);
+            } else {
+                __syncwarp();
+                if (lane == 0) mbar_arrive(x_empty0 + 8u * s);
+            }
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            sum_xn += __shfl_xor_sync(0xffffffffu, sum_xn, o);
+            n_refined += __shfl_xor_sync(0xffffffffu, n_refined, o);
+        }
+        if (lane == 0) {
+            if (p.acc && sum_xn != 0.0) atomicAdd(&p.acc[p.k * p.d + p.k], sum_xn);
+            if (n_refined) atomicAdd(&p.st->screen_refined, n_refined);
+        }
+    } else if (warp >= kUpdateWarp0 && p.acc) {
+        // ======================================== update ========================================
+        // Eight warps; warp u owns the labels [u*k/8, (u+1)*k/8) for the whole kernel, i.e. one contiguous
+        // range of each tile's label-sorted rows; lane = float4 column chunk.  No other thread ever touches
+        // an owner's (label, column) sums, so no atomics are needed anywhere in the tile loop.
+        const int u = warp - kUpdateWarp0;
+        const int ut = threadIdx.x - kUpdateWarp0 * 32;
+        double* sacc = (double*)(smem + p.off_acc);
+        const int nchunks = p.d >> 2;
+        const int l_lo = (u * p.k) >> 3, l_hi = ((u + 1) * p.k) >> 3;
+        const bool reg_path = p.k <= 32 && nchunks <= 32;
+        if (reg_path) {
+            // k <= 32: at most 4 owned labels.  Their FP32 sums live in registers (two packed pairs per
+            // label, added with FADD2) and are folded into the float64 shared accumulators every 8 tiles.
+            // Rows come in batches of 8 with predicated adds: a lone warp pays ~20 cycles per taken branch.
+            const bool active = lane < nchunks;
+            const int ch = active ? lane : 0;
+            const int a = ch >> 3;
+            const bool tail = a >= p.n_full;
+            const int col_off = (tail ? p.n_full : a) * kAtomBytes;
+            const int c16 = (tail ? (ch - p.n_full * 8) : (ch & 7)) << 4;
+            unsigned long long acc[4][2];
+            int cnt[4];
+#pragma unroll
+            for (int li = 0; li < 4; ++li) {
+                acc[li][0] = acc[li][1] = 0ull;
+                cnt[li] = 0;
+            }
+            auto fold = [&]() {
+#pragma unroll
+                for (int li = 0; li < 4; ++li) {
+                    if (l_lo + li < l_hi) {
+                        if (active) {
+                            double2* dst = reinterpret_cast<double2*>(sacc + (size_t)(l_lo + li) * p.d + ch * 4);
+                            const float2 lo = unpack2(acc[li][0]), hi = unpack2(acc[li][1]);
+                            double2 a0 = dst[0], a1 = dst[1];
+                            a0.x += (double)lo.x;
+                            a0.y += (double)lo.y;
+                            a1.x += (double)hi.x;
+                            a1.y += (double)hi.y;
+                            dst[0] = a0;
+                            dst[1] = a1;
+                        }
+                        if (lane == 0) sacc[p.k * p.d + l_lo + li] += (double)cnt[li];
+                        acc[li][0] = acc[li][1] = 0ull;
+                        cnt[li] = 0;
+                    }
+                }
+            };
+            int64_t it = 0;
+            for (int64_t tile = first_tile; tile < p.num_tiles; tile += tile_step, ++it) {
+                const int s = (int)(it % S);
+                const int sb = (int)(it & 1);
+                mbar_wait(s_full0 + 8u * sb, (uint32_t)((it >> 1) & 1));
+                mbar_wait(x_full0 + 8u * s, (uint32_t)((it / S) & 1));
+                if (ut == 0) trace_ev(p, it, 7);
+                const uint8_t* colp = smem + (size_t)s * stage_bytes + col_off;
+                // low halves of the perm words = byte offsets inside the atom
+                const unsigned short* perm = reinterpret_cast<const unsigned short*>(tail ? s_permT[sb] : s_perm[sb]);
+                int beg = s_base[sb][l_lo];
+#pragma unroll
+                for (int li = 0; li < 4; ++li) {
+                    if (l_lo + li < l_hi) {
+                        const int end = s_base[sb][l_lo + li + 1];
+#pragma unroll 1
+                        for (int base = beg; base < end; base += 8) {
+                            unsigned int w[8];
+                            ulonglong2 v[8];
+#pragma unroll
+                            for (int j = 0; j < 8; ++j) w[j] = perm[2 * (base + j)];  // past `end`: stale but valid offsets
+#pragma unroll
+                            for (int j = 0; j < 8; ++j) v[j] = *reinterpret_cast<const ulonglong2*>(colp + (w[j] ^ c16));
+#pragma unroll
+                            for (int j = 0; j < 8; ++j) {
+                                add2_if(acc[li][0], v[j].x, base + j, end);
+                                add2_if(acc[li][1], v[j].y, base + j, end);
+                            }
+                        }
+                        cnt[li] += end - beg;
+                        beg = end;
+                    }
+                }
+                __syncwarp();
+                if (lane == 0) {
+                    mbar_arrive(s_empty0 + 8u * sb);
+                    mbar_arrive(x_empty0 + 8u * s);
+                }
+                if (lane == 0) trace_ev(p, it, 8 + u);
+                if ((it & 7) == 7 || tile + tile_step >= p.num_tiles) fold();  // single (rare) fold site
+            }
+        } else {
+            // general shapes: flat walk over the owned range, run sums flushed when the next run opens
+            int64_t it = 0;
+            for (int64_t tile = first_tile; tile < p.num_tiles; tile += tile_step, ++it) {
+                const int s = (int)(it % S);
+                const int sb = (int)(it & 1);
+                mbar_wait(s_full0 + 8u * sb, (uint32_t)((it >> 1) & 1));
+                mbar_wait(x_full0 + 8u * s, (uint32_t)((it / S) & 1));
+                const uint8_t* stage = smem + (size_t)s * stage_bytes;
+                const int pb = s_base[sb][l_lo], pe = s_base[sb][l_hi];
+                for (int ch = lane; ch < nchunks; ch += 32) {
+                    const int a = ch >> 3;
+                    const bool tail = a >= p.n_full;
+                    const uint8_t* colp = stage + (tail ? p.n_full : a) * kAtomBytes;
+                    const int c16 = (tail ? (ch - p.n_full * 8) : (ch & 7)) << 4;
+                    const int* perm = tail ? s_permT[sb] : s_perm[sb];
+                    float4 r = make_float4(0.f, 0.f, 0.f, 0.f);
+                    int cur = -1;
+                    for (int pos = pb; pos <= pe; ++pos) {
+                        const int w = pos < pe ? perm[pos] : (1 << 16);
+                        if ((w & (1 << 16)) && cur >= 0) {  // a new run opens (or the range ends): flush (warp-uniform)
+                            double2* dst = reinterpret_cast<double2*>(sacc + (size_t)cur * p.d + ch * 4);
+                            double2 a0 = dst[0], a1 = dst[1];
+                            a0.x += (double)r.x;
+                            a0.y += (double)r.y;
+                            a1.x += (double)r.z;
+                            a1.y += (double)r.w;
+                            dst[0] = a0;
+                            dst[1] = a1;
+                            r = make_float4(0.f, 0.f, 0.f, 0.f);
+                        }
+                        if (pos < pe) {
+                            cur = w >> 17;
+                            const float4 v = *reinterpret_cast<const float4*>(colp + ((w & 0xFFFF) ^ c16));
+                            r.x += v.x;
+                            r.y += v.y;
+                            r.z += v.z;
+                            r.w += v.w;
+                        }
+                    }
+                }
+                for (int l = l_lo + lane; l < l_hi; l += 32)
+                    sacc[p.k * p.d + l] += (double)(s_base[sb][l + 1] - s_base[sb][l]);
+                __syncwarp();
+                if (lane == 0) {
+                    mbar_arrive(s_empty0 + 8u * sb);
+                    mbar_arrive(x_empty0 + 8u * s);
+                }
+            }
+        }
+        named_bar_sync(3, 256);
+        const int acc_n = p.k * p.d + p.k;
+#pragma unroll 1
+        for (int i = ut; i < acc_n; i += 256) {
+            const double v = sacc[i];
+            if (v != 0.0) atomicAdd(&p.acc[i], v);
+        }
+    }
+
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512));
+    }
+}
+
+// ---- host side ---------------------------------------------------------------------------------
+constexpr int kStaticSmem = 14 * 1024;  // upper bound of the kernel's static shared arrays
+
+struct Plan {
+    int k_pad, n_full, tail_cols, d_pad, num_stages, num_d, stage_bytes;
+    int off_c, off_acc, off_cn, off_xn, off_pd, off_bar, total;
+    bool ok;
+};
+
+Plan make_plan(int d, int k, bool with_acc) {
+    Plan pl = {};
+    pl.ok = false;
+    if (d <= 0 || k <= 0 || d > kMaxD || k > kMaxK || (d & 3)) return pl;
+    pl.k_pad = k <= 32 ? 32 : (k + 15) & ~15;  // k <= 32: the register-resident assign path wants 32 columns
+    // K-atoms: 32-float SWIZZLE_128B atoms, and a narrow SWIZZLE_32B / 64B tail when d % 32 is in 4..16
+    const int rem = d & 31;
+    pl.n_full = d >> 5;
+    pl.tail_cols = 0;
+    if (rem > 16) pl.n_full += 1;
+    else if (rem > 8) pl.tail_cols = 16;
+    else if (rem > 0) pl.tail_cols = 8;
+    pl.d_pad = pl.n_full * 32 + pl.tail_cols;
+    const int dcols = pl.k_pad <= 128 ? 2 * pl.k_pad : pl.k_pad;
+    pl.num_d = dcols <= 128 ? 4 : 2;  // score buffers of dcols TMEM columns each (512 columns in all)
+    pl.stage_bytes = pl.n_full * kAtomBytes + kTileM * pl.tail_cols * 4;
+    const int c_bytes = 2 * pl.k_pad * pl.d_pad * 4;
+    const int pd_bytes = k <= 32 ? 32 * 32 * 4 : 0;
+    const int acc_bytes = with_acc ? (int)((sizeof(double) * ((size_t)k * d + k) + 15) & ~(size_t)15) : 0;
+    const int fixed = c_bytes + pd_bytes + acc_bytes + pl.k_pad * 4 + 2 * kMaxStages * kTileM * 4 + 256 /*barriers*/ + 1024 /*align*/ +
+                      kStaticSmem;
+    int S = (kMaxSmem - fixed) / pl.stage_bytes;
+    if (S > kMaxStages) S = kMaxStages;
+    if (S < 2) return pl;
+    pl.num_stages = S;
+    int off = S * pl.stage_bytes;
+    off = (off + 1023) & ~1023;
+    pl.off_c = off;
+    off += c_bytes;
+    pl.off_acc = off;
+    off += acc_bytes;
+    pl.off_cn = off;
+    off += pl.k_pad * 4;
+    pl.off_xn = off;
+    off += 2 * kMaxStages * kTileM * 4;  // ||x||^2 and ||x - x^||^2 per stage
+    off = (off + 15) & ~15;
+    pl.off_pd = off;
+    off += pd_bytes;
+    pl.off_bar = off;
+    off += 256;
+    pl.total = off + 1024;
+    pl.ok = pl.total + kStaticSmem <= kMaxSmem;
+    return pl;
+}
+
+}  // namespace
+
+bool screen_supported(const float* X, int d, int k, bool with_acc) {
+    if ((reinterpret_cast<uintptr_t>(X) & 15) != 0) return false;
+    return make_plan(d, k, with_acc).ok;
+}
+size_t screen_workspace_bytes(int d, int k) {
+    Plan pl = make_plan(d, k, true);
+    return pl.ok ? sizeof(float) * (2 * (size_t)pl.k_pad * pl.d_pad + (size_t)k * k) : 0;
+}
+const char* screen_last_error() { return g_sc_err; }
+
+void screen_inertia_fix(const float* C, int k, int d, double* acc, cudaStream_t s) {
+    screen_inertia_fix_kernel<<<1, 256, 0, s>>>(C, k, d, acc);
+}
+
+int screen_pass(TcWorkspace* ws, const float* X, int64_t n, int d, int k, const float* C, const float* cnorm,
+                float* xnorm, float* xlo, bool xn_compute, int32_t* labels, double* acc, IterState* st,
+                bool honor_done, cudaStream_t s) {
+    const Plan pl = make_plan(d, k, acc != nullptr);
+    if (!pl.ok) {
+        snprintf(g_sc_err, sizeof(g_sc_err), "shape d=%d k=%d does not fit the tcgen05 screen kernel", d, k);
+        return 1;
+    }
+    const size_t need = sizeof(float) * 2 * (size_t)pl.k_pad * pl.d_pad;
+    if (need > ws->cap) {
+        if (ws->d_buf) cudaFree(ws->d_buf);
+        ws->d_buf = nullptr;
+        ws->cap = 0;
+        if (cudaMalloc(&ws->d_buf, need) != cudaSuccess) {
+            snprintf(g_sc_err, sizeof(g_sc_err), "cudaMalloc of %zu bytes for the TF32 centroids failed", need);
+            return 1;
+        }
+        ws->cap = need;
+    }
+    const size_t need_pd = sizeof(float) * (size_t)k * k;
+    if (need_pd > ws->pd_cap) {
+        if (ws->d_pd) cudaFree(ws->d_pd);
+        ws->d_pd = nullptr;
+        ws->pd_cap = 0;
+        if (cudaMalloc(&ws->d_pd, need_pd) != cudaSuccess) {
+            snprintf(g_sc_err, sizeof(g_sc_err), "cudaMalloc of %zu bytes for the centroid distance table failed", need_pd);
+            return 1;
+        }
+        ws->pd_cap = need_pd;
+    }
+    CUtensorMap tmX, tmXt, tmC, tmCt;
+    const uint32_t full_box = pl.n_full ? 32 : (uint32_t)pl.tail_cols;  // d < 32 with a narrow tail only
+    const uint32_t tail_box = pl.tail_cols ? (uint32_t)pl.tail_cols : full_box;
+    char* e = g_sc_err;
+    const size_t el = sizeof(g_sc_err);
+    if (encode_2d(e, el, &tmX, X, (uint64_t)d, (uint64_t)n, (uint64_t)d * 4, full_box, kTileM)) return 1;
+    if (encode_2d(e, el, &tmXt, X, (uint64_t)d, (uint64_t)n, (uint64_t)d * 4, tail_box, kTileM)) return 1;
+    if (encode_2d(e, el, &tmC, ws->d_buf, (uint64_t)pl.d_pad, (uint64_t)2 * pl.k_pad, (uint64_t)pl.d_pad * 4, full_box,
+                  (uint32_t)pl.k_pad))
+        return 1;
+    if (encode_2d(e, el, &tmCt, ws->d_buf, (uint64_t)pl.d_pad, (uint64_t)2 * pl.k_pad, (uint64_t)pl.d_pad * 4, tail_box,
+                  (uint32_t)pl.k_pad))
+        return 1;
+
+    static bool attr_set = false;
+    if (!attr_set) {
+        cudaFuncAttributes fa;
+        if (cudaFuncGetAttributes(&fa, kmeans_screen_kernel) != cudaSuccess || (int)fa.sharedSizeBytes > kStaticSmem) {
+            snprintf(g_sc_err, sizeof(g_sc_err), "unexpected static shared memory size of the screen kernel");
+            return 1;
+        }
+        const int max_dyn = kMaxSmem - (int)fa.sharedSizeBytes;
+        if (cudaFuncSetAttribute(kmeans_screen_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, max_dyn) !=
+            cudaSuccess) {
+            snprintf(g_sc_err, sizeof(g_sc_err), "cannot raise dynamic shared memory to %d bytes", max_dyn);
+            return 1;
+        }
+        attr_set = true;
+    }
+    launch_split_centroids(C, k, d, pl.k_pad, pl.d_pad, (float*)ws->d_buf, s);
+    pairdist_kernel<<<(k * k + 3) / 4, 128, 0, s>>>(C, k, d, (float*)ws->d_pd);
+    ScParams p;
+    p.n = n;
+    p.num_tiles = (n + kTileM - 1) / kTileM;
+    p.d = d;
+    p.k = k;
+    p.k_pad = pl.k_pad;
+    p.n_full = pl.n_full;
+    p.tail_cols = pl.tail_cols;
+    p.num_stages = pl.num_stages;
+    p.num_d = pl.num_d;
+    p.stage_bytes = pl.stage_bytes;
+    p.C = C;
+    p.cnorm = cnorm;
+    p.xnorm = xnorm;
+    p.xlo = xlo;
+    p.xn_compute = xn_compute ? 1 : 0;
+    p.labels = labels;
+    p.acc = acc;
+    p.st = st;
+    p.honor_done = honor_done ? 1 : 0;
+    // Error model (file header).  x is read truncated to TF32; ||x - x^||^2 is computed per row with the row
+    // norms (tol_x = slack for its FP32 rounding and the square root), and ||x - x^|| <= 2^-10 ||x|| (abs_rel).  Everything else is FP32 rounding: the tensor core adds
+    // each MMA's products into the FP32 accumulator with truncation (<= 1 ulp of the running sum per MMA,
+    // ceil(d/8) MMAs), the c_hi/c_lo split leaves 2^-22 |c|, and ||c||^2, ||x||^2 and the final FMAs round
+    // once each.  With 2|x||c| <= |x|^2+|c|^2 a margin (difference of two D_j) carries at most
+    // eps_rel * (||x||^2 + max||c||^2) of it; one D_j alone is off by at most abs_rel * (same scale).
+    p.pd = (const float*)ws->d_pd;
+    p.tol_x = 1.002f;
+    p.eps_rel = 2.f * (float)((d + 7) / 8 + 6) * 1.1920928955078125e-07f + 1e-6f;
+    p.abs_rel = 9.765625e-4f * 1.001f + p.eps_rel;
+    p.off_c = pl.off_c;
+    p.off_acc = pl.off_acc;
+    p.off_cn = pl.off_cn;
+    p.off_xn = pl.off_xn;
+    p.off_pd = pl.off_pd;
+    p.off_bar = pl.off_bar;
+    p.trace = nullptr;
+    const char* trace_path = getenv("B200KM_TRACE");
+    if (trace_path && acc) {
+        cudaMalloc((void**)&p.trace, 256 * 16 * sizeof(unsigned long long));
+        cudaMemsetAsync(p.trace, 0, 256 * 16 * sizeof(unsigned long long), s);
+    }
+    int64_t grid = p.num_tiles < kNumSMs ? p.num_tiles : kNumSMs;
+    if (grid < 1) grid = 1;
+    kmeans_screen_kernel<<<(unsigned)grid, kThreads, pl.total, s>>>(tmX, tmXt, tmC, tmCt, p);
+    cudaError_t err = cudaGetLastError();
+    if (err != cudaSuccess) {
+        snprintf(g_sc_err, sizeof(g_sc_err), "screen kernel launch failed: %s", cudaGetErrorString(err));
+        return 1;
+    }
+    if (p.trace) {  // development aid: synchronous dump of CTA 0's per-tile event clocks
+        static unsigned long long host[256 * 16];
+        cudaStreamSynchronize(s);
+        cudaMemcpy(host, p.trace, sizeof(host), cudaMemcpyDeviceToHost);
+        cudaFree(p.trace);
+        if (FILE* f = fopen(trace_path, "w")) {
+            for (int i = 0; i < 256; ++i) {
+                for (int j = 0; j < 16; ++j) fprintf(f, "%llu ", host[i * 16 + j]);
+                fprintf(f, "\n");
+            }
+            fclose(f);
+        }
+    }
+    return 0;
+}
+
+}  // namespace b200km

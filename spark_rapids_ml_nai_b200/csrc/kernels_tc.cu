@@ -20,6 +20,7 @@
 // This kernel replaces cuML's fusedL2NN + reduce_rows_by_key pair that runs behind reference
 // python/src/spark_rapids_ml/clustering.py:367-370 (fit) and :493-497 (predict).
 #include "tc.cuh"
+#include "tc_ptx.cuh"
 
 #include <cuda.h>
 
@@ -32,6 +33,8 @@
 namespace b200km {
 
 namespace {
+
+using namespace tcx;
 
 thread_local char g_tc_err[512] = "";
 
@@ -69,108 +72,6 @@ struct TcParams {
     int off_c, off_acc, off_cn, off_xn, off_bar;
 };
 
-// ---- PTX wrappers ------------------------------------------------------------------------------
-__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
-
-__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
-    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
-}
-__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
-    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
-}
-__device__ __forceinline__ void mbar_arrive_expect_tx(uint32_t bar, uint32_t bytes) {
-    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
-}
-// Blocking wait: try_wait suspends the warp in hardware (up to the time hint) until the phase completes,
-// so a waiting role costs no issue slots (a software poll loop measured ~9000 instructions per tile).
-// Not inlined: the kernel runs five instruction streams per SM and its hot code has to stay cache-resident.
-__device__ __noinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
-    asm volatile(
-        "{\n\t"
-        ".reg .pred p;\n\t"
-        "WAIT_LOOP:\n\t"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1, %2;\n\t"
-        "@p bra DONE;\n\t"
-        "bra WAIT_LOOP;\n\t"
-        "DONE:\n\t"
-        "}" ::"r"(bar),
-        "r"(parity), "r"(0x989680)
-        : "memory");
-}
-__device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* tm, uint32_t bar, int c0, int c1) {
-    asm volatile(
-        "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];" ::"r"(dst),
-        "l"(tm), "r"(bar), "r"(c0), "r"(c1)
-        : "memory");
-}
-__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
-__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
-__device__ __forceinline__ void tc_commit(uint32_t bar) {
-    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
-}
-// D[tmem] (+)= A[tmem] * B[smem desc], kind::tf32, M=128
-__device__ __forceinline__ void mma_tf32_ts(uint32_t d_tmem, uint32_t a_tmem, uint64_t b_desc, uint32_t idesc,
-                                            uint32_t accumulate) {
-    asm volatile(
-        "{\n\t"
-        ".reg .pred p;\n\t"
-        "setp.ne.b32 p, %4, 0;\n\t"
-        "tcgen05.mma.cta_group::1.kind::tf32 [%0], [%1], %2, %3, p;\n\t"
-        "}" ::"r"(d_tmem),
-        "r"(a_tmem), "l"(b_desc), "r"(idesc), "r"(accumulate)
-        : "memory");
-}
-__device__ __forceinline__ void tmem_st16(uint32_t taddr, const uint32_t (&r)[16]) {
-    asm volatile(
-        "tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, "
-        "%15, %16};" ::"r"(taddr),
-        "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]), "r"(r[8]), "r"(r[9]),
-        "r"(r[10]), "r"(r[11]), "r"(r[12]), "r"(r[13]), "r"(r[14]), "r"(r[15])
-        : "memory");
-}
-__device__ __forceinline__ void tmem_st8(uint32_t taddr, const uint32_t (&r)[16]) {
-    asm volatile("tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"r"(taddr), "r"(r[0]),
-                 "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7])
-                 : "memory");
-}
-__device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&r)[16]) {
-    asm volatile(
-        "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, "
-        "[%16];"
-        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
-          "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
-        : "r"(taddr)
-        : "memory");
-}
-__device__ __forceinline__ void tmem_wait_ld() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
-__device__ __forceinline__ void tmem_wait_st() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
-__device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
-    asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
-}
-__device__ __forceinline__ bool elect_one() {
-    uint32_t pred;
-    asm volatile(
-        "{\n\t"
-        ".reg .pred p;\n\t"
-        "elect.sync _|p, 0xffffffff;\n\t"
-        "selp.u32 %0, 1, 0, p;\n\t"
-        "}"
-        : "=r"(pred));
-    return pred != 0;
-}
-
-// K-major shared-memory matrix descriptor (sm_100 UMMA): start>>4 | LBO=1 | SBO = 8 rows | version 1 |
-// layout type (2 = SWIZZLE_128B, 4 = SWIZZLE_64B, 6 = SWIZZLE_32B); row_bytes = 128 / 64 / 32.
-__device__ __forceinline__ uint64_t make_b_desc(uint32_t smem_addr, int row_bytes) {
-    const uint64_t layout = row_bytes == 128 ? 2 : (row_bytes == 64 ? 4 : 6);
-    uint64_t desc = 0;
-    desc |= (uint64_t)((smem_addr >> 4) & 0x3FFF);
-    desc |= (uint64_t)1 << 16;
-    desc |= (uint64_t)((8 * row_bytes) >> 4) << 32;
-    desc |= (uint64_t)1 << 46;
-    desc |= layout << 61;
-    return desc;
-}
 
 // Byte offset of 16-byte chunk `chunk` (= float column / 4) of row r inside one tile stage.  Full atoms
 // use the TMA 128-byte swizzle (chunk ^= row & 7); the narrow tail atom the 64-byte (chunk ^= (row>>1)&3)
@@ -184,8 +85,6 @@ __device__ __forceinline__ uint32_t chunk_off(const TcParams& p, int r, int chun
     return base + (uint32_t)(r * 32 + ((c ^ ((r >> 2) & 1)) << 4));
 }
 
-__device__ __forceinline__ uint32_t tf32_trunc(uint32_t bits) { return bits & 0xFFFFE000u; }
-__device__ __forceinline__ uint32_t tf32_round(uint32_t bits) { return (bits + 0x1000u) & 0xFFFFE000u; }
 
 __device__ __forceinline__ void trace_ev(const TcParams& p, int64_t it, int ev) {
 #ifdef B200KM_ENABLE_TRACE
@@ -821,47 +720,6 @@ __global__ void __launch_bounds__(kThreads, 1)
     }
 }
 
-// ---- host side ---------------------------------------------------------------------------------
-typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
-                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
-                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
-
-EncodeTiledFn get_encode() {
-    static EncodeTiledFn fn = nullptr;
-    if (fn) return fn;
-    void* p = nullptr;
-    cudaDriverEntryPointQueryResult qres;
-    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres) != cudaSuccess ||
-        qres != cudaDriverEntryPointSuccess)
-        return nullptr;
-    fn = (EncodeTiledFn)p;
-    return fn;
-}
-
-// 2-D float32 tensor map, row-major [rows][cols]; box = box_cols x box_rows; the swizzle span equals the
-// box row (128 / 64 / 32 bytes).
-int encode_2d(CUtensorMap* tm, const void* base, uint64_t cols, uint64_t rows, uint64_t row_pitch_bytes,
-              uint32_t box_cols, uint32_t box_rows) {
-    EncodeTiledFn enc = get_encode();
-    if (!enc) {
-        snprintf(g_tc_err, sizeof(g_tc_err), "cuTensorMapEncodeTiled not available from the driver");
-        return 1;
-    }
-    cuuint64_t dims[2] = {cols, rows};
-    cuuint64_t strides[1] = {row_pitch_bytes};
-    cuuint32_t box[2] = {box_cols, box_rows};
-    cuuint32_t estr[2] = {1, 1};
-    const CUtensorMapSwizzle swz = box_cols == 32 ? CU_TENSOR_MAP_SWIZZLE_128B
-                                                  : (box_cols == 16 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_32B);
-    CUresult r = enc(tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<void*>(base), dims, strides, box, estr,
-                     CU_TENSOR_MAP_INTERLEAVE_NONE, swz, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
-                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-    if (r != CUDA_SUCCESS) {
-        snprintf(g_tc_err, sizeof(g_tc_err), "cuTensorMapEncodeTiled failed with CUresult %d", (int)r);
-        return 1;
-    }
-    return 0;
-}
 
 constexpr int kStaticSmem = 17 * 1024;  // upper bound of the kernel's static shared arrays
 
@@ -929,8 +787,18 @@ const char* tc_last_error() { return g_tc_err; }
 
 void tc_free(TcWorkspace* ws) {
     if (ws->d_buf) cudaFree(ws->d_buf);
+    if (ws->d_pd) cudaFree(ws->d_pd);
     ws->d_buf = nullptr;
+    ws->d_pd = nullptr;
     ws->cap = 0;
+    ws->pd_cap = 0;
+}
+
+void launch_split_centroids(const float* C, int k, int d, int k_pad, int d_pad, float* out, cudaStream_t s) {
+    const int total = k_pad * d_pad;
+    int blocks = (total + 255) / 256;
+    if (blocks > kNumSMs) blocks = kNumSMs;
+    split_centroids_kernel<<<blocks, 256, 0, s>>>(C, k, d, k_pad, d_pad, out);
 }
 
 int tc_pass(TcWorkspace* ws, const float* X, int64_t n, int d, int k, const float* C, const float* cnorm,
@@ -954,12 +822,12 @@ int tc_pass(TcWorkspace* ws, const float* X, int64_t n, int d, int k, const floa
     CUtensorMap tmX, tmXt, tmC, tmCt;
     const uint32_t full_box = pl.n_full ? 32 : (uint32_t)pl.tail_cols;   // d < 32 with a narrow tail only
     const uint32_t tail_box = pl.tail_cols ? (uint32_t)pl.tail_cols : full_box;
-    if (encode_2d(&tmX, X, (uint64_t)d, (uint64_t)n, (uint64_t)d * 4, full_box, kTileM)) return 1;
-    if (encode_2d(&tmXt, X, (uint64_t)d, (uint64_t)n, (uint64_t)d * 4, tail_box, kTileM)) return 1;
-    if (encode_2d(&tmC, ws->d_buf, (uint64_t)pl.d_pad, (uint64_t)2 * pl.k_pad, (uint64_t)pl.d_pad * 4, full_box,
+    if (encode_2d(g_tc_err, sizeof(g_tc_err), &tmX, X, (uint64_t)d, (uint64_t)n, (uint64_t)d * 4, full_box, kTileM)) return 1;
+    if (encode_2d(g_tc_err, sizeof(g_tc_err), &tmXt, X, (uint64_t)d, (uint64_t)n, (uint64_t)d * 4, tail_box, kTileM)) return 1;
+    if (encode_2d(g_tc_err, sizeof(g_tc_err), &tmC, ws->d_buf, (uint64_t)pl.d_pad, (uint64_t)2 * pl.k_pad, (uint64_t)pl.d_pad * 4, full_box,
                   (uint32_t)pl.k_pad))
         return 1;
-    if (encode_2d(&tmCt, ws->d_buf, (uint64_t)pl.d_pad, (uint64_t)2 * pl.k_pad, (uint64_t)pl.d_pad * 4, tail_box,
+    if (encode_2d(g_tc_err, sizeof(g_tc_err), &tmCt, ws->d_buf, (uint64_t)pl.d_pad, (uint64_t)2 * pl.k_pad, (uint64_t)pl.d_pad * 4, tail_box,
                   (uint32_t)pl.k_pad))
         return 1;
 
@@ -979,12 +847,7 @@ int tc_pass(TcWorkspace* ws, const float* X, int64_t n, int d, int k, const floa
         }
         attr_set = true;
     }
-    {
-        const int total = pl.k_pad * pl.d_pad;
-        int blocks = (total + 255) / 256;
-        if (blocks > kNumSMs) blocks = kNumSMs;
-        split_centroids_kernel<<<blocks, 256, 0, s>>>(C, k, d, pl.k_pad, pl.d_pad, (float*)ws->d_buf);
-    }
+    launch_split_centroids(C, k, d, pl.k_pad, pl.d_pad, (float*)ws->d_buf, s);
     TcParams p;
     p.n = n;
     p.num_tiles = (n + kTileM - 1) / kTileM;

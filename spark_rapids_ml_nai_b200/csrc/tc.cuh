@@ -7,7 +7,8 @@ namespace b200km {
 struct TcWorkspace {
     void* d_buf = nullptr;   // split centroids (hi | lo), padded, in the layout the MMA reads
     size_t cap = 0;
-    void* tmap_cache = nullptr;  // host-side cache of encoded tensor maps
+    void* d_pd = nullptr;    // [k][k] upper bounds of the pairwise centroid distances (screen kernel)
+    size_t pd_cap = 0;
 };
 
 bool tc_supported(const float* X, int d, int k, bool with_acc);
@@ -22,6 +23,21 @@ int tc_pass(TcWorkspace* ws, const float* X, int64_t n, int d, int k, const floa
             float* xnorm, bool xn_compute, int32_t* labels, float* best, double* acc, IterState* st,
             bool honor_done, cudaStream_t s);
 const char* tc_last_error();
+// out[2*k_pad][d_pad]: rows [0,k_pad) = centroids rounded to TF32, rows [k_pad,2k_pad) = the TF32-rounded
+// remainders; zero padded.  The B operand of both tcgen05 kernels.
+void launch_split_centroids(const float* C, int k, int d, int k_pad, int d_pad, float* out, cudaStream_t s);
+
+// Screen kernel (kernels_screen.cu): the same pass with the TF32 view of X read by the tensor cores straight
+// from shared memory, a rigorous error band and a float64 re-decision inside it.  Produces labels (optional)
+// and, when acc != nullptr, sums / counts and sum_i ||x_i||^2 in the inertia slot (screen_inertia_fix turns
+// that slot into the pass's inertia).  No per-row distances.
+bool screen_supported(const float* X, int d, int k, bool with_acc);
+size_t screen_workspace_bytes(int d, int k);
+int screen_pass(TcWorkspace* ws, const float* X, int64_t n, int d, int k, const float* C, const float* cnorm,
+                float* xnorm, float* xlo, bool xn_compute, int32_t* labels, double* acc, IterState* st,
+                bool honor_done, cudaStream_t s);
+void screen_inertia_fix(const float* C, int k, int d, double* acc, cudaStream_t s);
+const char* screen_last_error();
 void tc_free(TcWorkspace* ws);
 
 }  // namespace b200km

@@ -24,6 +24,10 @@ for (n, d, k) in shapes:
     bad = (lab != l_ref) & ~amb
     print(f"predict n={n} d={d} k={k}: path={h.last_path()} mismatches={bad.sum()} (ambiguous {amb.sum()}) "
           f"max|dist-best|={np.abs(dd - best).max():.3e} max best={best.max():.3e} t={time.time()-t0:.3f}s", flush=True)
+    lab_s, _ = h.predict(Xd, Cd, want_dist=False)   # labels only: the screen kernel
+    torch.cuda.synchronize()
+    bad_s = (lab_s.cpu().numpy() != l_ref) & ~amb
+    print(f"  screen predict: mismatches={bad_s.sum()}", flush=True)
     sums, counts, inertia, lab2 = h.lloyd_step(Xd, Cd, want_labels=True)
     torch.cuda.synchronize()
     lab2 = lab2.cpu().numpy()

@@ -1,0 +1,16 @@
+"""One traced lloyd_step on C2-like blobs with the true centres (development aid; needs a B200KM_ENABLE_TRACE build)."""
+import sys, os
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import torch
+from spark_rapids_ml_nai_b200 import _native
+n, d, k = 4_000_000, 100, 20
+dev = torch.device("cuda:0")
+g = torch.Generator(device=dev); g.manual_seed(1)
+centers = torch.rand((k, d), generator=g, device=dev) * 20.0 - 10.0
+lab = torch.randint(0, k, (n,), generator=g, device=dev)
+X = torch.randn((n, d), generator=g, device=dev) + centers[lab]
+h = _native.Handle(0)
+h.set_path(int(sys.argv[1]) if len(sys.argv) > 1 else _native.PATH_TC)
+C = centers.contiguous() if len(sys.argv) < 3 else X[torch.randperm(n, generator=g, device=dev)[:k]].clone()
+h.lloyd_step(X, C)
+torch.cuda.synchronize()
