@@ -295,6 +295,32 @@ __global__ void __launch_bounds__(kThreads, 1)
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
+    if (p.k <= 32) {
+        // per centroid: its nearest other centroid and the distances to the nearest and the second nearest one
+        // (the third-candidate test of the assign warps); written before any consumer can have a tile
+        if (threadIdx.x < 32) {
+            const float* pd_init = (const float*)(smem + p.off_pd);
+            float* nb = (float*)(smem + p.off_pd) + 32 * 32;
+            const int i = threadIdx.x;
+            float d1 = FLT_MAX, d2 = FLT_MAX;
+            int n1 = -1;
+            for (int j = 0; j < p.k; ++j) {
+                if (j == i) continue;
+                const float v = pd_init[i * 32 + j];
+                if (v < d1) {
+                    d2 = d1;
+                    d1 = v;
+                    n1 = j;
+                } else if (v < d2) {
+                    d2 = v;
+                }
+            }
+            nb[i] = d1;
+            nb[32 + i] = d2;
+            nb[64 + i] = __int_as_float(n1);
+        }
+        __syncthreads();
+    }
 
     const int64_t first_tile = blockIdx.x;
     const int64_t tile_step = gridDim.x;
@@ -494,23 +520,27 @@ __global__ void __launch_bounds__(kThreads, 1)
                 const float r1 = sqrtf(fmaxf(b1, 0.f) + p.abs_rel * scale);
                 const float safe = 4.f * t * r1 + eps;
                 const float margin = b2 - b1;
-                const bool flag0 = valid && p.k > 1 && margin < safe;
-                bool amb = false;
-                if (__any_sync(0xffffffffu, flag0)) {
-                    const float thr = b1 + safe;
+                // runner-up: the pair bound.  Any other centroid j can truly beat c_1 only if ||c_1 - c_j|| <= 2 r_1:
+                // impossible when even the nearest such centroid is farther than that; otherwise every other
+                // margin has to exceed `safe` (checked by counting the scores below best + safe).
+                const bool pair_ok = margin >= fminf(2.f * t * pd_s[i1 * 32 + i2] + eps, safe);
+                const float others = (__float_as_int(pd_s[32 * 32 + 64 + i1]) == i2) ? pd_s[32 * 32 + 32 + i1] : pd_s[32 * 32 + i1];
+                const bool third = others <= 2.f * r1 && margin < safe;  // a third candidate cannot be excluded yet
+                bool amb = valid && p.k > 1 && !pair_ok;
+                const float thr = b1 + safe;
+                if (__any_sync(0xffffffffu, valid && third)) {
                     int close = 0;
 #pragma unroll
                     for (int j = 0; j < 32; ++j) close += key[j] < thr ? 1 : 0;
-                    const bool pair_ok = margin >= 2.f * t * pd_s[i1 * 32 + i2] + eps;
-                    amb = flag0 && !(close == 2 && pair_ok);
-                    m = __ballot_sync(0xffffffffu, amb);
-                    if (m) {
+                    amb = amb || (valid && third && close > 2);
+                }
+                m = __ballot_sync(0xffffffffu, amb);
+                if (m) {
 #pragma unroll
-                        for (int j = 0; j < 32; ++j) {
-                            if (amb && key[j] < thr) {
-                                if (ncand < 4) s_cand[g][row][ncand] = (unsigned short)j;
-                                ++ncand;
-                            }
+                    for (int j = 0; j < 32; ++j) {
+                        if (amb && key[j] < thr) {
+                            if (ncand < 4) s_cand[g][row][ncand] = (unsigned short)j;
+                            ++ncand;
                         }
                     }
                 }
@@ -904,7 +934,7 @@ Plan make_plan(int d, int k, bool with_acc) {
     pl.num_d = dcols <= 128 ? 4 : 2;  // score buffers of dcols TMEM columns each (512 columns in all)
     pl.stage_bytes = pl.n_full * kAtomBytes + kTileM * pl.tail_cols * 4;
     const int c_bytes = 2 * pl.k_pad * pl.d_pad * 4;
-    const int pd_bytes = k <= 32 ? 32 * 32 * 4 : 0;
+    const int pd_bytes = k <= 32 ? (32 * 32 + 3 * 32) * 4 : 0;  // pair distances + per-centroid neighbour data
     const int acc_bytes = with_acc ? (int)((sizeof(double) * ((size_t)k * d + k) + 15) & ~(size_t)15) : 0;
     const int fixed = c_bytes + pd_bytes + acc_bytes + pl.k_pad * 4 + 2 * kMaxStages * kTileM * 4 + 256 /*barriers*/ + 1024 /*align*/ +
                       kStaticSmem;
