@@ -168,7 +168,7 @@ int ensure_ws(b200km_handle* h, int64_t n, int d, int k, bool need_row_bufs) {
         h->d_cnorm = nullptr;
         h->d_shift = nullptr;
         CU_TRY(cudaMalloc((void**)&h->d_cnorm, sizeof(float) * (k + 64)));
-        CU_TRY(cudaMalloc((void**)&h->d_shift, sizeof(double) * (k + 64)));
+        CU_TRY(cudaMalloc((void**)&h->d_shift, sizeof(double) * 2 * (k + 64)));  // shifts | cluster sizes
         h->k_cap = k + 64;
     }
     if (grow(&h->d_C, &h->kd_cap, kd)) return 1;
@@ -436,7 +436,7 @@ int b200km_fit(b200km_handle* h, const float* X, int64_t n_local, int d, int k, 
         if (run_pass(h, use_tc, X, n_local, d, k, h->d_C, nullptr, nullptr, h->d_acc, true, it == 0, s)) return 1;
         if (h->nranks > 1)
             NCCL_TRY(g_nccl.AllReduce(h->d_acc, h->d_acc, (size_t)acc_len, ncclFloat64, ncclSum, h->comm, s));
-        launch_finalize(h->d_C, k, d, h->d_cnorm, h->d_acc, h->d_shift, tol, h->d_state, s);
+        launch_finalize(h->d_C, k, d, h->d_cnorm, h->d_acc, h->d_shift, h->d_shift + h->k_cap, tol, h->d_state, s);
         h->launches += 1;
         CU_TRY(cudaGetLastError());
         CU_TRY(cudaMemcpyAsync(&h->h_state[slot], h->d_state, sizeof(IterState), cudaMemcpyDeviceToHost, s));

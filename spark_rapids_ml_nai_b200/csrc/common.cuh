@@ -14,6 +14,9 @@ struct IterState {
     double shift2;       // sum_j ||c_new_j - c_old_j||^2 of the last executed iteration
     float cnorm_max;     // max_j ||c_j||^2 of the current centroids
     unsigned int screen_refined;  // rows the screen kernel re-decided in float64 since the last prep
+    // k <= 32: labels owned by each of the 8 update warps of the screen kernel (4 slots per warp, -1 = none).
+    // Contiguous ranges after a centroid preparation; rebalanced by cluster size after every Lloyd iteration.
+    signed char own[32];
 };
 
 // Near-tie band: a row whose best and second-best approximate scores differ by less than
@@ -36,7 +39,7 @@ void launch_refine(const float* X, int64_t n, int d, const float* C, int k, int3
 void launch_update(const float* X, int64_t n, int d, int k, const int32_t* labels, const float* best,
                    double* acc, IterState* st, bool honor_done, cudaStream_t s);
 void launch_sum_best(const float* best, int64_t n, double* out, cudaStream_t s);
-void launch_finalize(float* C, int k, int d, float* cnorm, double* acc, double* shift_part,
+void launch_finalize(float* C, int k, int d, float* cnorm, double* acc, double* shift_part, double* cnt_part,
                      double tol, IterState* st, cudaStream_t s);
 
 }  // namespace b200km

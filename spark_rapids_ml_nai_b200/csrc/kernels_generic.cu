@@ -93,6 +93,10 @@ __global__ void __launch_bounds__(128) cnorm_kernel(const float* __restrict__ C,
             st->cnorm_max = fmaxf(fmaxf(red[0], red[1]), fmaxf(red[2], red[3]));
             st->amb_count = 0;
             st->screen_refined = 0;
+            for (int u = 0; u < 8; ++u) {
+                const int lo = (u * k) >> 3, hi = ((u + 1) * k) >> 3;
+                for (int li = 0; li < 4; ++li) st->own[u * 4 + li] = (k <= 32 && lo + li < hi) ? (signed char)(lo + li) : (signed char)-1;
+            }
             if (reset_iter) {
                 st->done = 0;
                 st->n_iter = 0;
@@ -435,8 +439,8 @@ __global__ void __launch_bounds__(256) sum_best_kernel(const float* __restrict__
 // shift^2 < tol and counts the iteration.
 __global__ void __launch_bounds__(128) finalize_kernel(float* __restrict__ C, int k, int d,
                                                        float* __restrict__ cnorm, double* __restrict__ acc,
-                                                       double* __restrict__ shift_part, double tol,
-                                                       IterState* st) {
+                                                       double* __restrict__ shift_part, double* __restrict__ cnt_part,
+                                                       double tol, IterState* st) {
     __shared__ double red_s[4];
     __shared__ float red_c[4];
     if (st->done) return;
@@ -464,6 +468,7 @@ __global__ void __launch_bounds__(128) finalize_kernel(float* __restrict__ C, in
     __syncthreads();
     if (threadIdx.x == 0) {
         shift_part[j] = (red_s[0] + red_s[1]) + (red_s[2] + red_s[3]);
+        cnt_part[j] = cnt;
         cnorm[j] = (red_c[0] + red_c[1]) + (red_c[2] + red_c[3]);
         acc[(size_t)k * d + j] = 0.0;
     }
@@ -491,6 +496,32 @@ __global__ void __launch_bounds__(128) finalize_kernel(float* __restrict__ C, in
             st->n_iter += 1;
             acc[(size_t)k * d + k] = 0.0;
             if (shift2 < tol) st->done = 1;
+            if (k <= 32) {
+                // update-warp ownership for the next pass: largest cluster first onto the least loaded warp
+                // with a free slot (the per-tile update time follows the rows a warp owns)
+                double load[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+                int used[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+                unsigned int taken = 0;
+                for (int q = 0; q < 32; ++q) st->own[q] = (signed char)-1;
+                for (int r = 0; r < k; ++r) {
+                    int best = -1;
+                    double bc = -1.0;
+                    for (int q = 0; q < k; ++q) {
+                        const double c = ((volatile double*)cnt_part)[q];
+                        if (!((taken >> q) & 1u) && c > bc) {
+                            bc = c;
+                            best = q;
+                        }
+                    }
+                    taken |= 1u << best;
+                    int w = -1;
+                    for (int u = 0; u < 8; ++u)
+                        if (used[u] < 4 && (w < 0 || load[u] < load[w])) w = u;
+                    st->own[w * 4 + used[w]] = (signed char)best;
+                    used[w] += 1;
+                    load[w] += bc;
+                }
+            }
         }
     }
 }
@@ -563,9 +594,9 @@ void launch_sum_best(const float* best, int64_t n, double* out, cudaStream_t s) 
     sum_best_kernel<<<(unsigned)blocks, 256, 0, s>>>(best, n, out);
 }
 
-void launch_finalize(float* C, int k, int d, float* cnorm, double* acc, double* shift_part, double tol,
-                     IterState* st, cudaStream_t s) {
-    finalize_kernel<<<k, 128, 0, s>>>(C, k, d, cnorm, acc, shift_part, tol, st);
+void launch_finalize(float* C, int k, int d, float* cnorm, double* acc, double* shift_part, double* cnt_part,
+                     double tol, IterState* st, cudaStream_t s) {
+    finalize_kernel<<<k, 128, 0, s>>>(C, k, d, cnorm, acc, shift_part, cnt_part, tol, st);
 }
 
 }  // namespace b200km

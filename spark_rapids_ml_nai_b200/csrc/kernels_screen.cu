@@ -56,7 +56,7 @@ constexpr int kMaxSmem = 227 * 1024;
 constexpr int kMaxStages = 4;
 constexpr int kMaxND = 4;
 constexpr int kMaxD = 256;
-constexpr int kMaxK = 256;
+constexpr int kMaxK = 128;  // larger k runs the split-TF32 kernel
 constexpr int kHist = kMaxK + 8;
 
 struct ScParams {
@@ -81,7 +81,7 @@ struct ScParams {
     float eps_rel;    // FP32 rounding terms of a margin, relative to ||x||^2 + max ||c||^2
     float abs_rel;    // bound of the error of one D_j, relative to ||x||^2 + max ||c||^2
     unsigned long long* trace;  // development aid (B200KM_TRACE)
-    int off_c, off_acc, off_cn, off_xn, off_pd, off_bar;
+    int off_c, off_acc, off_cn, off_xn, off_pd, off_cf, off_bar;  // off_cf < 0: no FP32 centroid copy
 };
 
 // D[tmem] (+)= A[smem desc] * B[smem desc], kind::tf32, M=128
@@ -278,6 +278,11 @@ __global__ void __launch_bounds__(kThreads, 1)
                 pd_init[i] = (a < p.k && b < p.k) ? p.pd[a * p.k + b] : 0.f;
             }
         }
+        if (p.off_cf >= 0) {
+            float* cf_init = (float*)(smem + p.off_cf);
+#pragma unroll 1
+            for (int i = threadIdx.x; i < p.k * p.d; i += kThreads) cf_init[i] = p.C[i];
+        }
         if (p.acc) {
             double* sacc_init = (double*)(smem + p.off_acc);
 #pragma unroll 1
@@ -462,7 +467,8 @@ __global__ void __launch_bounds__(kThreads, 1)
             const uint8_t* stage = smem + (size_t)s * stage_bytes;
             int label = 0;
             unsigned m = 0;   // lanes whose row needs the float64 look
-            int ncand = 0;    // candidates of this lane's row (listed in s_cand when <= 4)
+            int ncand = 0;    // candidates of this lane's row (listed in s_cand when <= 4; more: every centroid)
+            int ca = -1, cb = -1;  // the usual case: exactly the best and the runner-up, lower index first
             if (fast) {
                 // ---- k_pad <= 32: all scores stay in registers ----
                 uint32_t hi[32], lo[32];
@@ -494,23 +500,34 @@ __global__ void __launch_bounds__(kThreads, 1)
                         key[j] = __uint_as_float((__float_as_uint(dj) & ~31u) | (uint32_t)j);
                     }
                 }
-                // top-2 by a tournament of sorted pairs (independent operations, short dependency chains)
-                float m1[16], m2[16];
+                // the three smallest keys by a tournament of sorted lists (independent operations, short
+                // dependency chains): pairs -> triples -> ... ; the third smallest of two sorted triples is
+                // min(a3, b3, max(a1,b2), max(a2,b1))
+                float m1[16], m2[16], m3[8];
 #pragma unroll
                 for (int i = 0; i < 16; ++i) {
                     m1[i] = fminf(key[2 * i], key[2 * i + 1]);
                     m2[i] = fmaxf(key[2 * i], key[2 * i + 1]);
                 }
 #pragma unroll
-                for (int nn = 16; nn > 1; nn >>= 1) {
+                for (int i = 0; i < 8; ++i) {  // two sorted pairs -> sorted triple
+                    const float a1 = m1[2 * i], a2 = m2[2 * i], b1 = m1[2 * i + 1], b2 = m2[2 * i + 1];
+                    m1[i] = fminf(a1, b1);
+                    m2[i] = fminf(fmaxf(a1, b1), fminf(a2, b2));
+                    m3[i] = fminf(fmaxf(a1, b2), fmaxf(a2, b1));
+                }
+#pragma unroll
+                for (int nn = 8; nn > 1; nn >>= 1) {
 #pragma unroll
                     for (int i = 0; i < nn / 2; ++i) {
-                        const float a1 = m1[2 * i], a2 = m2[2 * i], b1 = m1[2 * i + 1], b2 = m2[2 * i + 1];
+                        const float a1 = m1[2 * i], a2 = m2[2 * i], a3 = m3[2 * i];
+                        const float b1 = m1[2 * i + 1], b2 = m2[2 * i + 1], b3 = m3[2 * i + 1];
                         m1[i] = fminf(a1, b1);
                         m2[i] = fminf(fmaxf(a1, b1), fminf(a2, b2));
+                        m3[i] = fminf(fminf(a3, b3), fminf(fmaxf(a1, b2), fmaxf(a2, b1)));
                     }
                 }
-                const float b1 = m1[0], b2 = m2[0];
+                const float b1 = m1[0], b2 = m2[0], b3 = m3[0];
                 const int i1 = (int)(__float_as_uint(b1) & 31u), i2 = (int)(__float_as_uint(b2) & 31u);
                 label = i1;
                 // safety test (see the file header); every quantity is an upper bound
@@ -521,29 +538,19 @@ __global__ void __launch_bounds__(kThreads, 1)
                 const float safe = 4.f * t * r1 + eps;
                 const float margin = b2 - b1;
                 // runner-up: the pair bound.  Any other centroid j can truly beat c_1 only if ||c_1 - c_j|| <= 2 r_1:
-                // impossible when even the nearest such centroid is farther than that; otherwise every other
-                // margin has to exceed `safe` (checked by counting the scores below best + safe).
+                // impossible when even the nearest such centroid is farther than that; otherwise the third best
+                // margin has to exceed `safe`.
                 const bool pair_ok = margin >= fminf(2.f * t * pd_s[i1 * 32 + i2] + eps, safe);
                 const float others = (__float_as_int(pd_s[32 * 32 + 64 + i1]) == i2) ? pd_s[32 * 32 + 32 + i1] : pd_s[32 * 32 + i1];
-                const bool third = others <= 2.f * r1 && margin < safe;  // a third candidate cannot be excluded yet
-                bool amb = valid && p.k > 1 && !pair_ok;
-                const float thr = b1 + safe;
-                if (__any_sync(0xffffffffu, valid && third)) {
-                    int close = 0;
-#pragma unroll
-                    for (int j = 0; j < 32; ++j) close += key[j] < thr ? 1 : 0;
-                    amb = amb || (valid && third && close > 2);
+                const bool third = valid && p.k > 2 && others <= 2.f * r1 &&
+                                   (b3 - b1) < safe + 7.63e-6f * fabsf(b3);  // a third candidate cannot be excluded
+                const bool amb = (valid && p.k > 1 && !pair_ok) || third;
+                if (amb && !third) {
+                    ca = min(i1, i2);
+                    cb = max(i1, i2);
                 }
+                if (third) ncand = 5;  // rare: the exact pass looks at every centroid
                 m = __ballot_sync(0xffffffffu, amb);
-                if (m) {
-#pragma unroll
-                    for (int j = 0; j < 32; ++j) {
-                        if (amb && key[j] < thr) {
-                            if (ncand < 4) s_cand[g][row][ncand] = (unsigned short)j;
-                            ++ncand;
-                        }
-                    }
-                }
             } else {
                 // ---- general k: 16 scores at a time, running (best, second, argmin), loose bound ----
                 float b1 = FLT_MAX, b2 = FLT_MAX;
@@ -609,6 +616,60 @@ __global__ void __launch_bounds__(kThreads, 1)
                 const int src = __ffs(m) - 1;
                 m &= m - 1;
                 const int rr = q * 32 + src;
+                const int ja = __shfl_sync(0xffffffffu, ca, src);
+                if (ja >= 0) {
+                    // two candidates: both distances in one sweep over the row
+                    const int jb = __shfl_sync(0xffffffffu, cb, src);
+                    const int nchunks = p.d >> 2;
+                    const float4* a4 = reinterpret_cast<const float4*>(p.C + (size_t)ja * p.d);
+                    const float4* b4 = reinterpret_cast<const float4*>(p.C + (size_t)jb * p.d);
+                    const float4* as4 = reinterpret_cast<const float4*>(smem + p.off_cf + (size_t)ja * p.d * 4);
+                    const float4* bs4 = reinterpret_cast<const float4*>(smem + p.off_cf + (size_t)jb * p.d * 4);
+                    float sa = 0.f, sb2 = 0.f;
+                    for (int ch = lane; ch < nchunks; ch += 32) {
+                        const float4 xv = *reinterpret_cast<const float4*>(stage + chunk_off(p, rr, ch));
+                        float4 av, bv;
+                        if (p.off_cf >= 0) {
+                            av = as4[ch];
+                            bv = bs4[ch];
+                        } else {
+                            av = __ldg(a4 + ch);
+                            bv = __ldg(b4 + ch);
+                        }
+                        const float a0 = xv.x - av.x, a1 = xv.y - av.y, a2 = xv.z - av.z, a3 = xv.w - av.w;
+                        const float e0 = xv.x - bv.x, e1 = xv.y - bv.y, e2 = xv.z - bv.z, e3 = xv.w - bv.w;
+                        sa += fmaf(a0, a0, a1 * a1) + fmaf(a2, a2, a3 * a3);
+                        sb2 += fmaf(e0, e0, e1 * e1) + fmaf(e2, e2, e3 * e3);
+                    }
+#pragma unroll
+                    for (int o = 16; o > 0; o >>= 1) {
+                        sa += __shfl_xor_sync(0xffffffffu, sa, o);
+                        sb2 += __shfl_xor_sync(0xffffffffu, sb2, o);
+                    }
+                    int bi = sb2 < sa ? jb : ja;  // a tie keeps the lower index
+                    if (fabsf(sa - sb2) <= 4e-6f * (sa + sb2)) {
+                        // float64 (rare)
+                        double da = 0.0, db2 = 0.0;
+                        for (int i = lane; i < p.d; i += 32) {
+                            const double xv = (double)*reinterpret_cast<const float*>(stage + chunk_off(p, rr, i >> 2) + ((i & 3) << 2));
+                            const double fa = xv - (double)__ldg(p.C + (size_t)ja * p.d + i);
+                            const double fb = xv - (double)__ldg(p.C + (size_t)jb * p.d + i);
+                            da = fma(fa, fa, da);
+                            db2 = fma(fb, fb, db2);
+                        }
+#pragma unroll
+                        for (int o = 16; o > 0; o >>= 1) {
+                            da += __shfl_xor_sync(0xffffffffu, da, o);
+                            db2 += __shfl_xor_sync(0xffffffffu, db2, o);
+                        }
+                        bi = db2 < da ? jb : ja;
+                    }
+                    if (lane == src) {
+                        label = bi;
+                        ++n_refined;
+                    }
+                    continue;
+                }
                 const int nc = __shfl_sync(0xffffffffu, ncand, src);
                 const int total = nc <= 4 ? nc : p.k;  // more than 4 candidates: scan every centroid
                 const int nchunks = p.d >> 2;
@@ -767,6 +828,9 @@ __global__ void __launch_bounds__(kThreads, 1)
             // k <= 32: at most 4 owned labels.  Their FP32 sums live in registers (two packed pairs per
             // label, added with FADD2) and are folded into the float64 shared accumulators every 8 tiles.
             // Rows come in batches of 8 with predicated adds: a lone warp pays ~20 cycles per taken branch.
+            int lab[4];  // owned labels (-1 = free slot): balanced by cluster size, see IterState::own
+#pragma unroll
+            for (int li = 0; li < 4; ++li) lab[li] = p.st->own[u * 4 + li];
             const bool active = lane < nchunks;
             const int ch = active ? lane : 0;
             const int a = ch >> 3;
@@ -783,9 +847,9 @@ __global__ void __launch_bounds__(kThreads, 1)
             auto fold = [&]() {
 #pragma unroll
                 for (int li = 0; li < 4; ++li) {
-                    if (l_lo + li < l_hi) {
+                    if (lab[li] >= 0) {
                         if (active) {
-                            double2* dst = reinterpret_cast<double2*>(sacc + (size_t)(l_lo + li) * p.d + ch * 4);
+                            double2* dst = reinterpret_cast<double2*>(sacc + (size_t)lab[li] * p.d + ch * 4);
                             const float2 lo = unpack2(acc[li][0]), hi = unpack2(acc[li][1]);
                             double2 a0 = dst[0], a1 = dst[1];
                             a0.x += (double)lo.x;
@@ -795,7 +859,7 @@ __global__ void __launch_bounds__(kThreads, 1)
                             dst[0] = a0;
                             dst[1] = a1;
                         }
-                        if (lane == 0) sacc[p.k * p.d + l_lo + li] += (double)cnt[li];
+                        if (lane == 0) sacc[p.k * p.d + lab[li]] += (double)cnt[li];
                         acc[li][0] = acc[li][1] = 0ull;
                         cnt[li] = 0;
                     }
@@ -811,11 +875,10 @@ __global__ void __launch_bounds__(kThreads, 1)
                 const uint8_t* colp = smem + (size_t)s * stage_bytes + col_off;
                 // low halves of the perm words = byte offsets inside the atom
                 const unsigned short* perm = reinterpret_cast<const unsigned short*>(tail ? s_permT[sb] : s_perm[sb]);
-                int beg = s_base[sb][l_lo];
 #pragma unroll
                 for (int li = 0; li < 4; ++li) {
-                    if (l_lo + li < l_hi) {
-                        const int end = s_base[sb][l_lo + li + 1];
+                    if (lab[li] >= 0) {
+                        const int beg = s_base[sb][lab[li]], end = s_base[sb][lab[li] + 1];
 #pragma unroll 1
                         for (int base = beg; base < end; base += 8) {
                             unsigned int w[8];
@@ -831,7 +894,6 @@ __global__ void __launch_bounds__(kThreads, 1)
                             }
                         }
                         cnt[li] += end - beg;
-                        beg = end;
                     }
                 }
                 __syncwarp();
@@ -909,11 +971,11 @@ __global__ void __launch_bounds__(kThreads, 1)
 }
 
 // ---- host side ---------------------------------------------------------------------------------
-constexpr int kStaticSmem = 14 * 1024;  // upper bound of the kernel's static shared arrays
+constexpr int kStaticSmem = 9 * 1024;  // upper bound of the kernel's static shared arrays
 
 struct Plan {
     int k_pad, n_full, tail_cols, d_pad, num_stages, num_d, stage_bytes;
-    int off_c, off_acc, off_cn, off_xn, off_pd, off_bar, total;
+    int off_c, off_acc, off_cn, off_xn, off_pd, off_cf, off_bar, total;
     bool ok;
 };
 
@@ -955,6 +1017,12 @@ Plan make_plan(int d, int k, bool with_acc) {
     off = (off + 15) & ~15;
     pl.off_pd = off;
     off += pd_bytes;
+    // an FP32 copy of the centroids for the exact re-decision when there is room left (else they come from L2)
+    const int cf_bytes = k * d * 4;
+    const bool cf_fits = kMaxSmem - fixed - S * pl.stage_bytes >= cf_bytes + 64;
+    pl.off_cf = cf_fits ? off : -1;
+    if (cf_fits) off += cf_bytes;
+    off = (off + 15) & ~15;
     pl.off_bar = off;
     off += 256;
     pl.total = off + 1024;
@@ -1074,6 +1142,7 @@ int screen_pass(TcWorkspace* ws, const float* X, int64_t n, int d, int k, const 
     p.off_cn = pl.off_cn;
     p.off_xn = pl.off_xn;
     p.off_pd = pl.off_pd;
+    p.off_cf = pl.off_cf;
     p.off_bar = pl.off_bar;
     p.trace = nullptr;
     const char* trace_path = getenv("B200KM_TRACE");
