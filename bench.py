@@ -42,7 +42,7 @@ def parse_args():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--config", default="c2", choices=sorted(CONFIGS))
     ap.add_argument("--rows", type=int, default=0, help="override total rows (debug only; marks the line)")
-    ap.add_argument("--path", default="auto", choices=["auto", "ffma", "tc"])
+    ap.add_argument("--path", default="auto", choices=["auto", "ffma", "tc", "tc_split"])
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--e2e-rows", type=int, default=0, help="rows per rank for the e2e leg (default: the shard)")
@@ -193,7 +193,8 @@ def main():
         dist.broadcast_object_list(obj, src=0)
         uid = obj[0]
     h = _native.Handle(device=local_rank, rank=rank, nranks=world, uid=uid)
-    h.set_path({"auto": _native.PATH_AUTO, "ffma": _native.PATH_FFMA, "tc": _native.PATH_TC}[args.path])
+    h.set_path({"auto": _native.PATH_AUTO, "ffma": _native.PATH_FFMA, "tc": _native.PATH_TC,
+                "tc_split": _native.PATH_TC_SPLIT}[args.path])
 
     X = gen_blobs_device(torch, n_local, d, k, seed=1, rank=rank, device=device)
     init = h.init_centroids(X, k, mode=_native.INIT_RANDOM, seed=1)
@@ -223,6 +224,7 @@ def main():
     ms = ev0.elapsed_time(ev1)
     kern_ms, kern_n, launches = h.profile_read()
     h.profile_enable(False)
+    refined_rows, last_kernel = h.screen_stats()
     clocks = sampler.stop() if rank == 0 else None
     assert n_iter == args.steps, (n_iter, args.steps)
     t = torch.tensor([ms], dtype=torch.float64, device=device)
@@ -239,13 +241,15 @@ def main():
         kms = kern_ms / kern_n
         achieved = (4.0 * d * n_local) / (kms * 1e-3) / 1e9
         traffic = None
+        kernel = {0: "assign_ffma_kernel", 1: "kmeans_fused_tc_kernel", 2: "kmeans_screen_kernel"}[last_kernel]
         tpath = os.path.join(ROOT, "profiles", "r01_traffic.json")
-        if path == "tc" and os.path.exists(tpath):
-            t = json.load(open(tpath))["kmeans_fused_tc"]
-            if (t["d"], t["k"]) == (d, k):  # bytes per row from the committed ncu capture, scaled to this launch
+        if os.path.exists(tpath):
+            t = json.load(open(tpath)).get(kernel)
+            if t and (t["d"], t["k"]) == (d, k):  # bytes per row from the committed ncu capture, scaled to this launch
                 traffic = (t["dram_bytes_read"] + t["dram_bytes_write"]) / t["rows"] * n_local
         roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                    "traffic": traffic, "kernel": "kmeans_fused_tc" if path == "tc" else "assign_ffma_kernel",
+                    "traffic": traffic, "kernel": kernel,
+                    "rows_decided_exactly_per_pass": refined_rows / max(1, args.steps),
                     "kernel_ms": kms, "launches_timed": kern_n, "peak_source": peak_src,
                     "algorithmic_bytes_per_launch": 4.0 * d * n_local}
 
@@ -318,7 +322,9 @@ def main():
                        "l2": f"per-GPU input {n_local * d * 4 / 1e9:.2f} GB " +
                              ("is larger than the 126 MB L2, no flush needed" if n_local * d * 4 > 4e8
                               else "FITS in L2: latency-bound config, flagged"),
-                       "arithmetic": "fp32 data; 3xTF32 (tc) or FP32 FFMA products; float64 sums"},
+                       "arithmetic": "fp32 data; tc: TF32 tensor-core screen with a rigorous error bound, rows inside "
+                                     "it decided exactly (FP32 differences / float64); ffma: FP32 products; "
+                                     "float64 sums"},
             "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks,
         }
         print(json.dumps(line), flush=True)

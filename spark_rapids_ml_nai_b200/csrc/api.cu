@@ -229,7 +229,7 @@ int run_pass(b200km_handle* h, bool use_tc, const float* X, int64_t n, int d, in
         h->last_kernel = screen ? 2 : 1;
         if (rec) CU_TRY(cudaEventRecord(h->pev[2 * h->prof_n + 1], s));
         if (rec) h->prof_n++;
-        h->launches += 2;  // operand preparation + the fused kernel
+        h->launches += screen ? 3 : 2;  // operand preparation (+ centroid distance table) + the fused kernel
         return 0;
     }
     if (!labels) labels = h->d_labels;
