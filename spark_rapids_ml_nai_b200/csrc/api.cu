@@ -219,7 +219,8 @@ int run_pass(b200km_handle* h, bool use_tc, const float* X, int64_t n, int d, in
         const bool screen = h->path != B200KM_PATH_TC_SPLIT && !h->split_only && best == nullptr &&
                             screen_supported(X, d, k, acc != nullptr);
         if (screen) {
-            if (screen_pass(&h->tc, X, n, d, k, C, h->d_cnorm, h->d_xnorm, (float*)h->d_work, xn_compute, labels, acc, h->d_state,
+            if (screen_pass(&h->tc, X, n, d, k, C, h->d_cnorm, h->d_xnorm, (float*)h->d_work, (unsigned int*)h->d_best,
+                            xn_compute, labels, acc, h->d_state,
                             honor_done, s))
                 return fail("tcgen05 screen pass failed: %s", screen_last_error());
         } else if (tc_pass(&h->tc, X, n, d, k, C, h->d_cnorm, h->d_xnorm, xn_compute, labels, best, acc, h->d_state,
@@ -229,7 +230,7 @@ int run_pass(b200km_handle* h, bool use_tc, const float* X, int64_t n, int d, in
         h->last_kernel = screen ? 2 : 1;
         if (rec) CU_TRY(cudaEventRecord(h->pev[2 * h->prof_n + 1], s));
         if (rec) h->prof_n++;
-        h->launches += screen ? 3 : 2;  // operand preparation (+ centroid distance table) + the fused kernel
+        h->launches += screen ? 4 : 2;  // operand preparation (+ distance table, exact fix-up) + the fused kernel
         return 0;
     }
     if (!labels) labels = h->d_labels;

@@ -59,6 +59,14 @@ constexpr int kMaxD = 256;
 constexpr int kMaxK = 128;  // larger k runs the split-TF32 kernel
 constexpr int kHist = kMaxK + 8;
 
+// Per-row verdict written by the screen kernel: bits 0-7 the computed best centroid (the row's provisional
+// label, already counted in the sums), bits 8-15 the runner-up, bits 16-17 what the exact pass has to look at,
+// bit 31 "not decided by the TF32 scores".
+constexpr unsigned int kInfoUnsafe = 1u << 31;
+constexpr unsigned int kInfoPair = 0u << 16;   // exactly the best and the runner-up
+constexpr unsigned int kInfoReach = 1u << 16;  // every centroid within 2 r_1 of the computed best
+constexpr unsigned int kInfoAll = 2u << 16;    // every centroid
+
 struct ScParams {
     int64_t n;
     int64_t num_tiles;
@@ -73,6 +81,7 @@ struct ScParams {
     float* xlo;    // [n] ||x - trunc_tf32(x)||^2: likewise
     int xn_compute;
     int32_t* labels;  // may be null
+    unsigned int* info;  // [n] per-row verdict of the screen (see kInfo*): read by screen_fixup_kernel
     double* acc;      // [k*d | k | 1] or null (labels-only pass)
     IterState* st;
     int honor_done;
@@ -81,7 +90,7 @@ struct ScParams {
     float eps_rel;    // FP32 rounding terms of a margin, relative to ||x||^2 + max ||c||^2
     float abs_rel;    // bound of the error of one D_j, relative to ||x||^2 + max ||c||^2
     unsigned long long* trace;  // development aid (B200KM_TRACE)
-    int off_c, off_acc, off_cn, off_xn, off_pd, off_cf, off_bar;  // off_cf < 0: no FP32 centroid copy
+    int off_c, off_acc, off_cn, off_xn, off_pd, off_bar;
 };
 
 // D[tmem] (+)= A[smem desc] * B[smem desc], kind::tf32, M=128
@@ -186,6 +195,119 @@ __global__ void __launch_bounds__(256) screen_inertia_fix_kernel(const float* __
     }
 }
 
+// Exact decision of the rows the screen left open (bit 31 of their info word), straight from HBM: one warp per
+// row, lane = float4 column chunk; FP32 squared differences (no cancellation: their error is ~2^-21 of the
+// distance itself), float64 when even those tie; ties keep the lowest index.  A row whose exact label differs
+// from the provisional one is moved between the float64 sums.  These rows are few (C2: < 1 %), and keeping this
+// code out of the persistent kernel keeps that kernel's instruction stream hot.
+__device__ __forceinline__ float sqdist_f32(const float4* __restrict__ x4, const float4* __restrict__ c4, int nchunks,
+                                            int lane) {
+    float s = 0.f;
+    for (int ch = lane; ch < nchunks; ch += 32) {
+        const float4 xv = __ldg(x4 + ch), cv = __ldg(c4 + ch);
+        const float d0 = xv.x - cv.x, d1 = xv.y - cv.y, d2 = xv.z - cv.z, d3 = xv.w - cv.w;
+        s += fmaf(d0, d0, d1 * d1) + fmaf(d2, d2, d3 * d3);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+    return s;
+}
+__device__ __forceinline__ double sqdist_f64(const float* __restrict__ x, const float* __restrict__ c, int d, int lane) {
+    double s = 0.0;
+    for (int i = lane; i < d; i += 32) {
+        const double df = (double)__ldg(x + i) - (double)__ldg(c + i);
+        s = fma(df, df, s);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+    return s;
+}
+
+__global__ void __launch_bounds__(256) screen_fixup_kernel(const float* __restrict__ X, int64_t n, int d, int k,
+                                                           const float* __restrict__ C, const float* __restrict__ pd,
+                                                           const unsigned int* __restrict__ info,
+                                                           int32_t* __restrict__ labels, double* __restrict__ acc,
+                                                           IterState* st, int honor_done) {
+    if (honor_done && st->done) return;
+    const int lane = threadIdx.x & 31;
+    const int64_t warp0 = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    const int64_t nwarps = (int64_t)gridDim.x * (blockDim.x >> 5);
+    const int nchunks = d >> 2;
+    unsigned int decided = 0;
+    for (int64_t base = warp0 * 32; base < n; base += nwarps * 32) {
+        const int64_t r = base + lane;
+        const unsigned int w = r < n ? info[r] : 0u;
+        unsigned m = __ballot_sync(0xffffffffu, (w & kInfoUnsafe) != 0u);
+        decided += __popc(m);
+        while (m) {
+            const int src = __ffs(m) - 1;
+            m &= m - 1;
+            const unsigned int word = __shfl_sync(0xffffffffu, w, src);
+            const int64_t row = base + src;
+            const int i1 = (int)(word & 255u), i2 = (int)((word >> 8) & 255u);
+            const unsigned int mode = word & (3u << 16);
+            const float* x = X + (size_t)row * d;
+            const float4* x4 = reinterpret_cast<const float4*>(x);
+            int bi;
+            if (mode == kInfoPair) {
+                const int ja = min(i1, i2), jb = max(i1, i2);
+                const float sa = sqdist_f32(x4, reinterpret_cast<const float4*>(C + (size_t)ja * d), nchunks, lane);
+                const float sb = sqdist_f32(x4, reinterpret_cast<const float4*>(C + (size_t)jb * d), nchunks, lane);
+                bi = sb < sa ? jb : ja;
+                if (fabsf(sa - sb) <= 4e-6f * (sa + sb)) {
+                    const double da = sqdist_f64(x, C + (size_t)ja * d, d, lane);
+                    const double db = sqdist_f64(x, C + (size_t)jb * d, d, lane);
+                    bi = db < da ? jb : ja;
+                }
+            } else {
+                // every centroid, or those that can beat the computed best c_1 at all: ||c_1 - c_j|| <= 2 ||x - c_1||
+                float reach = FLT_MAX;
+                if (mode == kInfoReach)
+                    reach = 2.f * sqrtf(sqdist_f32(x4, reinterpret_cast<const float4*>(C + (size_t)i1 * d), nchunks, lane)) * 1.0001f;
+                float f1 = FLT_MAX, f2 = FLT_MAX;
+                bi = i1;
+                for (int j = 0; j < k; ++j) {
+                    if (j != i1 && reach < FLT_MAX && pd[(size_t)i1 * k + j] > reach) continue;
+                    const float sum = sqdist_f32(x4, reinterpret_cast<const float4*>(C + (size_t)j * d), nchunks, lane);
+                    if (sum < f1) {  // ascending index order: ties keep the lowest
+                        f2 = f1;
+                        f1 = sum;
+                        bi = j;
+                    } else {
+                        f2 = fminf(f2, sum);
+                    }
+                }
+                if (f2 < FLT_MAX && (f2 - f1) <= 4e-6f * (f1 + f2)) {
+                    double bd = DBL_MAX;
+                    for (int j = 0; j < k; ++j) {
+                        if (j != i1 && reach < FLT_MAX && pd[(size_t)i1 * k + j] > reach) continue;
+                        const double sum = sqdist_f64(x, C + (size_t)j * d, d, lane);
+                        if (sum < bd) {
+                            bd = sum;
+                            bi = j;
+                        }
+                    }
+                }
+            }
+            if (bi != i1) {
+                if (labels && lane == 0) labels[row] = bi;
+                if (acc) {  // move the row from its provisional cluster to the exact one
+                    for (int i = lane; i < d; i += 32) {
+                        const double v = (double)__ldg(x + i);
+                        atomicAdd(&acc[(size_t)bi * d + i], v);
+                        atomicAdd(&acc[(size_t)i1 * d + i], -v);
+                    }
+                    if (lane == 0) {
+                        atomicAdd(&acc[(size_t)k * d + bi], 1.0);
+                        atomicAdd(&acc[(size_t)k * d + i1], -1.0);
+                    }
+                }
+            }
+        }
+    }
+    if (lane == 0 && decided) atomicAdd(&st->screen_refined, decided);
+}
+
 // ||x||^2 and ||x - trunc_tf32(x)||^2 of one row of the tile in `stage` (interleaved partial sums)
 __device__ __forceinline__ void acc_norms(const float4 v, float (&s)[4], float (&l)[4]) {
     const float e[4] = {v.x, v.y, v.z, v.w};
@@ -220,7 +342,6 @@ __global__ void __launch_bounds__(kThreads, 1)
     extern __shared__ uint8_t smem_raw[];
     __shared__ uint8_t s_hist[2][2][4][kHist];         // per assign group, double-buffered by tile: per-warp label counts
     __shared__ unsigned short s_off[2][4][kHist];      // per assign group: per-warp start offsets (only when k >= 32)
-    __shared__ unsigned short s_cand[2][kTileM][4];    // per assign group: candidate centroids of near-tie rows
     __shared__ unsigned short s_base[2][kHist];        // start of every label's run in the sorted order (double-buffered)
     __shared__ int s_perm[2][kTileM + 8];   // sorted position -> low 16 bits: row offset in a full atom
                                             // (r*128 | swizzle); bit 16: first row of its run; bits 17+: label
@@ -277,11 +398,6 @@ __global__ void __launch_bounds__(kThreads, 1)
                 const int a = i >> 5, b = i & 31;
                 pd_init[i] = (a < p.k && b < p.k) ? p.pd[a * p.k + b] : 0.f;
             }
-        }
-        if (p.off_cf >= 0) {
-            float* cf_init = (float*)(smem + p.off_cf);
-#pragma unroll 1
-            for (int i = threadIdx.x; i < p.k * p.d; i += kThreads) cf_init[i] = p.C[i];
         }
         if (p.acc) {
             double* sacc_init = (double*)(smem + p.off_acc);
@@ -446,7 +562,6 @@ __global__ void __launch_bounds__(kThreads, 1)
         const int sb = g;
 
         double sum_xn = 0.0;
-        unsigned int n_refined = 0;
         for (int64_t it = g;; it += 2) {
             const int64_t tile = first_tile + it * tile_step;
             if (tile >= p.num_tiles) break;
@@ -464,11 +579,8 @@ __global__ void __launch_bounds__(kThreads, 1)
             if (et == 0) trace_ev(p, it, 4);
 
             const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(db * dcols);
-            const uint8_t* stage = smem + (size_t)s * stage_bytes;
             int label = 0;
-            unsigned m = 0;   // lanes whose row needs the float64 look
-            int ncand = 0;    // candidates of this lane's row (listed in s_cand when <= 4; more: every centroid)
-            int ca = -1, cb = -1;  // the usual case: exactly the best and the runner-up, lower index first
+            unsigned int verdict = 0;  // this row's info word
             if (fast) {
                 // ---- k_pad <= 32: all scores stay in registers ----
                 uint32_t hi[32], lo[32];
@@ -478,7 +590,6 @@ __global__ void __launch_bounds__(kThreads, 1)
                 tc_fence_before();
                 __syncwarp();
                 if (lane == 0) mbar_arrive(d_empty0 + 8u * db);  // the score buffer is free again
-                mbar_wait(x_full0 + 8u * s, (uint32_t)((it / S) & 1));  // TMA writes visible to this thread
                 if (p.xn_compute) {
                     mbar_wait(xn_full0 + 8u * s, (uint32_t)((it / S) & 1));
                     xn = xn_s[s * kTileM + row];
@@ -545,12 +656,7 @@ __global__ void __launch_bounds__(kThreads, 1)
                 const bool third = valid && p.k > 2 && others <= 2.f * r1 &&
                                    (b3 - b1) < safe + 7.63e-6f * fabsf(b3);  // a third candidate cannot be excluded
                 const bool amb = (valid && p.k > 1 && !pair_ok) || third;
-                if (amb && !third) {
-                    ca = min(i1, i2);
-                    cb = max(i1, i2);
-                }
-                if (third) ncand = 5;  // rare: the exact pass looks at every centroid
-                m = __ballot_sync(0xffffffffu, amb);
+                verdict = (unsigned)i1 | ((unsigned)i2 << 8) | (amb ? kInfoUnsafe | (third ? kInfoReach : kInfoPair) : 0u);
             } else {
                 // ---- general k: 16 scores at a time, running (best, second, argmin), loose bound ----
                 float b1 = FLT_MAX, b2 = FLT_MAX;
@@ -574,7 +680,6 @@ __global__ void __launch_bounds__(kThreads, 1)
                         }
                     }
                 }
-                mbar_wait(x_full0 + 8u * s, (uint32_t)((it / S) & 1));  // TMA writes visible to this thread
                 if (p.xn_compute) {
                     mbar_wait(xn_full0 + 8u * s, (uint32_t)((it / S) & 1));
                     xn = xn_s[s * kTileM + row];
@@ -583,144 +688,16 @@ __global__ void __launch_bounds__(kThreads, 1)
                 // 2|x||c| <= |x|^2 + |c|^2: the pair bound with ||c_a - c_b|| <= 2 max||c||
                 const float band = (2.f * p.abs_rel + p.eps_rel) * (xn + cmax);
                 const bool amb = valid && p.k > 1 && (b2 - b1) < band;
-                m = __ballot_sync(0xffffffffu, amb);
-                // near-tie rows: a second look at the scores lists the candidates inside the band (first 4 kept)
-                if (m) {
-#pragma unroll 1
-                    for (int c0 = 0; c0 < p.k; c0 += 16) {
-                        uint32_t r[16], r2[16];
-                        tmem_ld16(taddr + c0, r);
-                        if (stacked) tmem_ld16(taddr + p.k_pad + c0, r2);
-                        tmem_wait_ld();
-#pragma unroll
-                        for (int j = 0; j < 16; ++j) {
-                            float dot = __uint_as_float(r[j]);
-                            if (stacked) dot += __uint_as_float(r2[j]);
-                            const float sc = fmaf(-2.f, dot, cn_s[c0 + j]);
-                            if (amb && (c0 + j) < p.k && (sc - b1) < band) {
-                                if (ncand < 4) s_cand[g][row][ncand] = (unsigned short)(c0 + j);
-                                ++ncand;
-                            }
-                        }
-                    }
-                }
+                verdict = ((unsigned)i1 & 255u) | (amb ? kInfoUnsafe | kInfoAll : 0u);
                 tc_fence_before();
                 __syncwarp();
                 if (lane == 0) mbar_arrive(d_empty0 + 8u * db);
             }
 
-            // ---- exact re-decision, warp-cooperative: lane = float4 column chunk of the row.  FP32 squared
-            // differences first (no cancellation: their error is ~2^-21 of the distance itself); a margin
-            // inside that error is settled in float64. ----
-            while (m) {
-                const int src = __ffs(m) - 1;
-                m &= m - 1;
-                const int rr = q * 32 + src;
-                const int ja = __shfl_sync(0xffffffffu, ca, src);
-                if (ja >= 0) {
-                    // two candidates: both distances in one sweep over the row
-                    const int jb = __shfl_sync(0xffffffffu, cb, src);
-                    const int nchunks = p.d >> 2;
-                    const float4* a4 = reinterpret_cast<const float4*>(p.C + (size_t)ja * p.d);
-                    const float4* b4 = reinterpret_cast<const float4*>(p.C + (size_t)jb * p.d);
-                    const float4* as4 = reinterpret_cast<const float4*>(smem + p.off_cf + (size_t)ja * p.d * 4);
-                    const float4* bs4 = reinterpret_cast<const float4*>(smem + p.off_cf + (size_t)jb * p.d * 4);
-                    float sa = 0.f, sb2 = 0.f;
-                    for (int ch = lane; ch < nchunks; ch += 32) {
-                        const float4 xv = *reinterpret_cast<const float4*>(stage + chunk_off(p, rr, ch));
-                        float4 av, bv;
-                        if (p.off_cf >= 0) {
-                            av = as4[ch];
-                            bv = bs4[ch];
-                        } else {
-                            av = __ldg(a4 + ch);
-                            bv = __ldg(b4 + ch);
-                        }
-                        const float a0 = xv.x - av.x, a1 = xv.y - av.y, a2 = xv.z - av.z, a3 = xv.w - av.w;
-                        const float e0 = xv.x - bv.x, e1 = xv.y - bv.y, e2 = xv.z - bv.z, e3 = xv.w - bv.w;
-                        sa += fmaf(a0, a0, a1 * a1) + fmaf(a2, a2, a3 * a3);
-                        sb2 += fmaf(e0, e0, e1 * e1) + fmaf(e2, e2, e3 * e3);
-                    }
-#pragma unroll
-                    for (int o = 16; o > 0; o >>= 1) {
-                        sa += __shfl_xor_sync(0xffffffffu, sa, o);
-                        sb2 += __shfl_xor_sync(0xffffffffu, sb2, o);
-                    }
-                    int bi = sb2 < sa ? jb : ja;  // a tie keeps the lower index
-                    if (fabsf(sa - sb2) <= 4e-6f * (sa + sb2)) {
-                        // float64 (rare)
-                        double da = 0.0, db2 = 0.0;
-                        for (int i = lane; i < p.d; i += 32) {
-                            const double xv = (double)*reinterpret_cast<const float*>(stage + chunk_off(p, rr, i >> 2) + ((i & 3) << 2));
-                            const double fa = xv - (double)__ldg(p.C + (size_t)ja * p.d + i);
-                            const double fb = xv - (double)__ldg(p.C + (size_t)jb * p.d + i);
-                            da = fma(fa, fa, da);
-                            db2 = fma(fb, fb, db2);
-                        }
-#pragma unroll
-                        for (int o = 16; o > 0; o >>= 1) {
-                            da += __shfl_xor_sync(0xffffffffu, da, o);
-                            db2 += __shfl_xor_sync(0xffffffffu, db2, o);
-                        }
-                        bi = db2 < da ? jb : ja;
-                    }
-                    if (lane == src) {
-                        label = bi;
-                        ++n_refined;
-                    }
-                    continue;
-                }
-                const int nc = __shfl_sync(0xffffffffu, ncand, src);
-                const int total = nc <= 4 ? nc : p.k;  // more than 4 candidates: scan every centroid
-                const int nchunks = p.d >> 2;
-                float f1 = FLT_MAX, f2 = FLT_MAX;
-                int bi = 0;
-                for (int t = 0; t < total; ++t) {
-                    const int j = nc <= 4 ? (int)s_cand[g][rr][t] : t;
-                    const float4* c4 = reinterpret_cast<const float4*>(p.C + (size_t)j * p.d);
-                    float sum = 0.f;
-                    for (int ch = lane; ch < nchunks; ch += 32) {
-                        const float4 xv = *reinterpret_cast<const float4*>(stage + chunk_off(p, rr, ch));
-                        const float4 cv = __ldg(c4 + ch);
-                        const float d0 = xv.x - cv.x, d1 = xv.y - cv.y, d2 = xv.z - cv.z, d3 = xv.w - cv.w;
-                        sum += fmaf(d0, d0, d1 * d1) + fmaf(d2, d2, d3 * d3);
-                    }
-#pragma unroll
-                    for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
-                    if (sum < f1) {  // candidates come in ascending index order: ties keep the lowest
-                        f2 = f1;
-                        f1 = sum;
-                        bi = j;
-                    } else {
-                        f2 = fminf(f2, sum);
-                    }
-                }
-                if (total > 1 && (f2 - f1) <= 4e-6f * (f1 + f2)) {
-                    // float64 (rare)
-                    double bd = DBL_MAX;
-                    for (int t = 0; t < total; ++t) {
-                        const int j = nc <= 4 ? (int)s_cand[g][rr][t] : t;
-                        const float* c = p.C + (size_t)j * p.d;
-                        double sum = 0.0;
-                        for (int i = lane; i < p.d; i += 32) {
-                            const float xv = *reinterpret_cast<const float*>(stage + chunk_off(p, rr, i >> 2) + ((i & 3) << 2));
-                            const double df = (double)xv - (double)__ldg(c + i);
-                            sum = fma(df, df, sum);
-                        }
-#pragma unroll
-                        for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
-                        if (sum < bd) {
-                            bd = sum;
-                            bi = j;
-                        }
-                    }
-                }
-                if (lane == src) {
-                    label = bi;
-                    ++n_refined;
-                }
-            }
+            // the verdict goes out with the row; unsafe rows keep the computed best as a provisional label (also in
+            // the sums) until screen_fixup_kernel has decided them exactly
             if (valid) {
+                p.info[grow] = verdict;
                 if (p.labels) p.labels[grow] = label;
                 sum_xn += (double)xn;
             }
@@ -807,11 +784,9 @@ __global__ void __launch_bounds__(kThreads, 1)
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) {
             sum_xn += __shfl_xor_sync(0xffffffffu, sum_xn, o);
-            n_refined += __shfl_xor_sync(0xffffffffu, n_refined, o);
         }
         if (lane == 0) {
             if (p.acc && sum_xn != 0.0) atomicAdd(&p.acc[p.k * p.d + p.k], sum_xn);
-            if (n_refined) atomicAdd(&p.st->screen_refined, n_refined);
         }
     } else if (warp >= kUpdateWarp0 && p.acc) {
         // ======================================== update ========================================
@@ -975,7 +950,7 @@ constexpr int kStaticSmem = 9 * 1024;  // upper bound of the kernel's static sha
 
 struct Plan {
     int k_pad, n_full, tail_cols, d_pad, num_stages, num_d, stage_bytes;
-    int off_c, off_acc, off_cn, off_xn, off_pd, off_cf, off_bar, total;
+    int off_c, off_acc, off_cn, off_xn, off_pd, off_bar, total;
     bool ok;
 };
 
@@ -1017,12 +992,6 @@ Plan make_plan(int d, int k, bool with_acc) {
     off = (off + 15) & ~15;
     pl.off_pd = off;
     off += pd_bytes;
-    // an FP32 copy of the centroids for the exact re-decision when there is room left (else they come from L2)
-    const int cf_bytes = k * d * 4;
-    const bool cf_fits = kMaxSmem - fixed - S * pl.stage_bytes >= cf_bytes + 64;
-    pl.off_cf = cf_fits ? off : -1;
-    if (cf_fits) off += cf_bytes;
-    off = (off + 15) & ~15;
     pl.off_bar = off;
     off += 256;
     pl.total = off + 1024;
@@ -1047,8 +1016,8 @@ void screen_inertia_fix(const float* C, int k, int d, double* acc, cudaStream_t 
 }
 
 int screen_pass(TcWorkspace* ws, const float* X, int64_t n, int d, int k, const float* C, const float* cnorm,
-                float* xnorm, float* xlo, bool xn_compute, int32_t* labels, double* acc, IterState* st,
-                bool honor_done, cudaStream_t s) {
+                float* xnorm, float* xlo, unsigned int* info, bool xn_compute, int32_t* labels, double* acc,
+                IterState* st, bool honor_done, cudaStream_t s) {
     const Plan pl = make_plan(d, k, acc != nullptr);
     if (!pl.ok) {
         snprintf(g_sc_err, sizeof(g_sc_err), "shape d=%d k=%d does not fit the tcgen05 screen kernel", d, k);
@@ -1124,6 +1093,7 @@ int screen_pass(TcWorkspace* ws, const float* X, int64_t n, int d, int k, const 
     p.xlo = xlo;
     p.xn_compute = xn_compute ? 1 : 0;
     p.labels = labels;
+    p.info = info;
     p.acc = acc;
     p.st = st;
     p.honor_done = honor_done ? 1 : 0;
@@ -1142,7 +1112,6 @@ int screen_pass(TcWorkspace* ws, const float* X, int64_t n, int d, int k, const 
     p.off_cn = pl.off_cn;
     p.off_xn = pl.off_xn;
     p.off_pd = pl.off_pd;
-    p.off_cf = pl.off_cf;
     p.off_bar = pl.off_bar;
     p.trace = nullptr;
     const char* trace_path = getenv("B200KM_TRACE");
@@ -1157,6 +1126,13 @@ int screen_pass(TcWorkspace* ws, const float* X, int64_t n, int d, int k, const 
     if (err != cudaSuccess) {
         snprintf(g_sc_err, sizeof(g_sc_err), "screen kernel launch failed: %s", cudaGetErrorString(err));
         return 1;
+    }
+    {
+        int64_t blocks = (n + 255) / 256;
+        if (blocks > kNumSMs * 8) blocks = kNumSMs * 8;
+        if (blocks < 1) blocks = 1;
+        screen_fixup_kernel<<<(unsigned)blocks, 256, 0, s>>>(X, n, d, k, C, (const float*)ws->d_pd, info, labels, acc, st,
+                                                             honor_done ? 1 : 0);
     }
     if (p.trace) {  // development aid: synchronous dump of CTA 0's per-tile event clocks
         static unsigned long long host[256 * 16];

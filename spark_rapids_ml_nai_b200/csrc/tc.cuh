@@ -34,8 +34,8 @@ void launch_split_centroids(const float* C, int k, int d, int k_pad, int d_pad, 
 bool screen_supported(const float* X, int d, int k, bool with_acc);
 size_t screen_workspace_bytes(int d, int k);
 int screen_pass(TcWorkspace* ws, const float* X, int64_t n, int d, int k, const float* C, const float* cnorm,
-                float* xnorm, float* xlo, bool xn_compute, int32_t* labels, double* acc, IterState* st,
-                bool honor_done, cudaStream_t s);
+                float* xnorm, float* xlo, unsigned int* info, bool xn_compute, int32_t* labels, double* acc,
+                IterState* st, bool honor_done, cudaStream_t s);
 void screen_inertia_fix(const float* C, int k, int d, double* acc, cudaStream_t s);
 const char* screen_last_error();
 void tc_free(TcWorkspace* ws);
