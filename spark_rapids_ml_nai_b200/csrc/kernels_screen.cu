@@ -6,28 +6,33 @@
 //      tile (the tensor core reads the top 19 bits of each word, i.e. x truncated to TF32), B = the stacked
 //      TF32 split [c_hi ; c_lo] of the centroids, FP32 accumulation in TMEM; the assign warps form
 //      D_j = ||x||^2 + ||c_j||^2 - 2 x^.c_j;
-//   2. decides which rows the TF32 view of x cannot decide.  With x^ = trunc(x), ||x - x^|| <= 2^-10 ||x||,
-//      so the error of a MARGIN D_a - D_b is bounded by 2 * 2^-10 ||x|| * ||c_a - c_b|| (+ the FP32 rounding
-//      terms): it scales with the distance between the two centroids, not with their norms.  A centroid j
-//      can truly beat the computed best c_1 only if ||c_1 - c_j|| <= 2 r_1 (r_1 = distance to c_1), hence a
-//      row is safe when its runner-up margin exceeds the bound for the pair (table of pairwise centroid
-//      distances) and every other margin exceeds 4 * 2^-10 ||x|| r_1.  Any other row is re-decided exactly
-//      in float64 from the tile in shared memory - labels are exact for every row;
+//   2. decides which rows the TF32 view of x decides.  With x^ = trunc(x) the error of a MARGIN D_a - D_b is
+//      2 (x - x^).(c_a - c_b) plus FP32 rounding, hence bounded by 2 ||x - x^|| ||c_a - c_b|| + eps: it scales
+//      with the distance between the two centroids (a k x k table), not with their norms, and ||x - x^|| is the
+//      row's own value (computed with the row norms), not the 2^-10 ||x|| worst case.  A centroid j can truly
+//      beat the computed best c_1 only if ||c_1 - c_j|| <= 2 r_1 (r_1 = distance to c_1); so a row is decided
+//      when its runner-up margin exceeds the pair's bound and either no other centroid is that close to c_1
+//      (each centroid's nearest-neighbour distances) or the third-best margin exceeds 4 ||x - x^|| r_1 + eps.
+//      Every row leaves a verdict word; the open rows keep the computed best as a provisional label;
 //   3. sorts the tile's rows by label and adds them (exact FP32 data, not the TF32 view) into per-cluster
 //      sums held in registers / float64 shared memory.
-// Nothing but labels leaves the kernel per row.  The inertia of the pass follows exactly from the float64
-// sums:  sum_i ||x_i - c_l(i)||^2 = sum_i ||x_i||^2 - 2 sum_j c_j.S_j + sum_j n_j ||c_j||^2  (screen_inertia_fix).
+// screen_fixup_kernel then decides the open rows exactly from HBM (FP32 squared differences, float64 when even
+// those tie) and moves a row between the float64 sums when its exact label differs - labels and sums are exact
+// for every row.  Keeping that rarely executed code out of the persistent kernel matters: inside it, one such
+// row cost 1400-2400 cycles of an assign warp (instruction fetch of cold code), 0.9 % of the rows cost 30 %.
+// The inertia of the pass follows from the float64 sums:
+//   sum_i ||x_i - c_l(i)||^2 = sum_i ||x_i||^2 - 2 sum_j c_j.S_j + sum_j n_j ||c_j||^2     (screen_inertia_fix).
 //
-// When too many rows need the float64 look (structureless data) b200km_fit switches to the split-TF32 kernel
-// (kernels_tc.cu), which also splits x and therefore needs no re-decision beyond FP32 rounding.
+// When too many rows stay open (structureless data) b200km_fit switches to the split-TF32 kernel
+// (kernels_tc.cu), which also splits x and therefore leaves nothing open beyond FP32 rounding.
 //
 // Warp roles (704 threads, 1 CTA per SM, grid = #SMs):
 //   warp 0       TMA producer (centroids once, then X tiles: 32-float SWIZZLE_128B K-atoms + a narrow tail)
 //   warp 1       TMEM allocator + MMA issuer (warp-uniform loop, one elected lane, A and B via UMMA descriptors)
-//   warps 2-5    row norms ||x||^2 (first pass of a fit only; later passes read them back from HBM)
-//   warps 6-13   assign, two groups taking alternate tiles: tcgen05.ld, top-2, safety test, float64
-//                re-decision, counting sort by label
-//   warps 14-21  update: label-sorted accumulation; warp = label range, lane = float4 column chunk
+//   warps 2-5    row norms ||x||^2 and ||x - x^||^2 (first pass of a fit only; later passes read them back)
+//   warps 6-13   assign, two groups taking alternate tiles: tcgen05.ld, three smallest scores by a tournament,
+//                verdict, stable counting sort of the tile by label
+//   warps 14-21  update: label-sorted accumulation; a warp owns <= 4 labels, lane = float4 column chunk
 //
 // Replaces cuML's fusedL2NN + reduce_rows_by_key pair behind reference
 // python/src/spark_rapids_ml/clustering.py:367-370 (fit) and :493-497 (predict).
