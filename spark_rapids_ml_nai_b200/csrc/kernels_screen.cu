@@ -61,8 +61,8 @@ constexpr int kMaxSmem = 227 * 1024;
 constexpr int kMaxStages = 4;
 constexpr int kMaxND = 4;
 constexpr int kMaxD = 256;
-constexpr int kMaxK = 128;  // larger k runs the split-TF32 kernel
-constexpr int kHist = kMaxK + 8;
+constexpr int kMaxK = 32;  // the scores of a row live in registers; larger k runs the split-TF32 kernel
+constexpr int kHist = 40;  // label bins (k + 1) rounded up
 
 // Per-row verdict written by the screen kernel: bits 0-7 the computed best centroid (the row's provisional
 // label, already counted in the sums), bits 8-15 the runner-up, bits 16-17 what the exact pass has to look at,
@@ -346,7 +346,6 @@ __global__ void __launch_bounds__(kThreads, 1)
 
     extern __shared__ uint8_t smem_raw[];
     __shared__ uint8_t s_hist[2][2][4][kHist];         // per assign group, double-buffered by tile: per-warp label counts
-    __shared__ unsigned short s_off[2][4][kHist];      // per assign group: per-warp start offsets (only when k >= 32)
     __shared__ unsigned short s_base[2][kHist];        // start of every label's run in the sorted order (double-buffered)
     __shared__ int s_perm[2][kTileM + 8];   // sorted position -> low 16 bits: row offset in a full atom
                                             // (r*128 | swizzle); bit 16: first row of its run; bits 17+: label
@@ -360,8 +359,7 @@ __global__ void __launch_bounds__(kThreads, 1)
     const int ND = p.num_d;  // power of two
     const int stage_bytes = p.stage_bytes;
     const int c_block = 2 * p.k_pad * 128;  // bytes of one full-atom block [c_hi rows | c_lo rows]
-    const bool stacked = p.k_pad <= 128;
-    const int dcols = stacked ? 2 * p.k_pad : p.k_pad;
+    const int dcols = 2 * p.k_pad;  // TMEM columns of one score buffer: c_hi products | c_lo products
 
     // barrier table
     const uint32_t bar0 = smem_base + p.off_bar;
@@ -484,8 +482,8 @@ __global__ void __launch_bounds__(kThreads, 1)
         // code costs ~100 cycles per instruction, ~40 from warp-uniform code: tools/mma_bench.cu).  Both
         // operands come from shared memory: A = the X tile exactly as TMA wrote it (K-major, swizzled), B =
         // the TF32 centroids; consecutive K-steps differ only in the descriptors' start address (+32 B).
-        // k_pad <= 128: B is the stacked block [c_hi ; c_lo] (N = 2*k_pad, one instruction per K-step; the
-        // assign warps add the two halves); larger k: two instructions per K-step into the same columns.
+        // B is the stacked block [c_hi ; c_lo] (N = 2*k_pad, one instruction per K-step; the assign warps add
+        // the two halves).
         const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(kTileM >> 4) << 24) |
                                ((uint32_t)(dcols >> 3) << 17);
         const int tail_row_bytes = p.tail_cols ? p.tail_cols * 4 : 128;
@@ -493,8 +491,6 @@ __global__ void __launch_bounds__(kThreads, 1)
         const uint64_t bdesc_tail = make_b_desc(smem_base + p.off_c + p.n_full * c_block, tail_row_bytes);
         const uint64_t adesc_full = make_b_desc(smem_base, 128);
         const uint64_t adesc_tail = make_b_desc(smem_base + p.n_full * kAtomBytes, tail_row_bytes);
-        const uint64_t lo_full = (uint64_t)((p.k_pad * 128) >> 4);             // c_lo rows inside an atom block
-        const uint64_t lo_tail = (uint64_t)((p.k_pad * tail_row_bytes) >> 4);
         const int tail_steps = p.tail_cols >> 3;
         mbar_wait(c_full, 0);
         int64_t it = 0;
@@ -514,7 +510,6 @@ __global__ void __launch_bounds__(kThreads, 1)
 #pragma unroll
                     for (int kk = 0; kk < 4; ++kk) {
                         mma_tf32_ss(d_tmem, ad + 2 * kk, bd + 2 * kk, idesc, (a | kk) != 0);
-                        if (!stacked) mma_tf32_ss(d_tmem, ad + 2 * kk, bd + lo_full + 2 * kk, idesc, 1);
                     }
                     ad += (uint64_t)(kAtomBytes >> 4);
                     bd += (uint64_t)(c_block >> 4);
@@ -522,7 +517,6 @@ __global__ void __launch_bounds__(kThreads, 1)
 #pragma unroll 1
                 for (int kk = 0; kk < tail_steps; ++kk) {
                     mma_tf32_ss(d_tmem, adesc_tail + soff + 2 * kk, bdesc_tail + 2 * kk, idesc, (p.n_full | kk) != 0);
-                    if (!stacked) mma_tf32_ss(d_tmem, adesc_tail + soff + 2 * kk, bdesc_tail + lo_tail + 2 * kk, idesc, 1);
                 }
                 tc_commit(d_full0 + 8u * db);
                 trace_ev(p, it, 2);
@@ -563,7 +557,6 @@ __global__ void __launch_bounds__(kThreads, 1)
         float* xn_s = (float*)(smem + p.off_xn);
         const float cmax = p.st->cnorm_max;
         const float* pd_s = (const float*)(smem + p.off_pd);
-        const bool fast = stacked && p.k_pad <= 32;
         const int sb = g;
 
         double sum_xn = 0.0;
@@ -586,118 +579,81 @@ __global__ void __launch_bounds__(kThreads, 1)
             const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(db * dcols);
             int label = 0;
             unsigned int verdict = 0;  // this row's info word
-            if (fast) {
-                // ---- k_pad <= 32: all scores stay in registers ----
-                uint32_t hi[32], lo[32];
-                tmem_ld32(taddr, hi);
-                tmem_ld32(taddr + 32, lo);
-                tmem_wait_ld();
-                tc_fence_before();
-                __syncwarp();
-                if (lane == 0) mbar_arrive(d_empty0 + 8u * db);  // the score buffer is free again
-                if (p.xn_compute) {
-                    mbar_wait(xn_full0 + 8u * s, (uint32_t)((it / S) & 1));
-                    xn = xn_s[s * kTileM + row];
-                    xl = xn_s[(kMaxStages + s) * kTileM + row];
+            // ---- k_pad <= 32: all scores stay in registers ----
+            uint32_t hi[32], lo[32];
+            tmem_ld32(taddr, hi);
+            tmem_ld32(taddr + 32, lo);
+            tmem_wait_ld();
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(d_empty0 + 8u * db);  // the score buffer is free again
+            if (p.xn_compute) {
+                mbar_wait(xn_full0 + 8u * s, (uint32_t)((it / S) & 1));
+                xn = xn_s[s * kTileM + row];
+                xl = xn_s[(kMaxStages + s) * kTileM + row];
+            }
+            // keys: D_j = ||x||^2 + ||c_j||^2 - 2 x^.c_j with the centroid index in the 5 low mantissa bits
+            // (a perturbation below 2^-18 |D_j|, covered by the bound)
+            float key[32];
+            const float4* cn4 = reinterpret_cast<const float4*>(cn_s);
+#pragma unroll
+            for (int j4 = 0; j4 < 8; ++j4) {
+                const float4 c = cn4[j4];
+                const float cc[4] = {c.x, c.y, c.z, c.w};
+#pragma unroll
+                for (int t = 0; t < 4; ++t) {
+                    const int j = j4 * 4 + t;
+                    const float dot = __uint_as_float(hi[j]) + __uint_as_float(lo[j]);
+                    const float dj = fmaf(-2.f, dot, cc[t] + xn);  // padded columns: FLT_MAX
+                    key[j] = __uint_as_float((__float_as_uint(dj) & ~31u) | (uint32_t)j);
                 }
-                // keys: D_j = ||x||^2 + ||c_j||^2 - 2 x^.c_j with the centroid index in the 5 low mantissa bits
-                // (a perturbation below 2^-18 |D_j|, covered by the bound)
-                float key[32];
-                const float4* cn4 = reinterpret_cast<const float4*>(cn_s);
+            }
+            // the three smallest keys by a tournament of sorted lists (independent operations, short
+            // dependency chains): pairs -> triples -> ... ; the third smallest of two sorted triples is
+            // min(a3, b3, max(a1,b2), max(a2,b1))
+            float m1[16], m2[16], m3[8];
 #pragma unroll
-                for (int j4 = 0; j4 < 8; ++j4) {
-                    const float4 c = cn4[j4];
-                    const float cc[4] = {c.x, c.y, c.z, c.w};
+            for (int i = 0; i < 16; ++i) {
+                m1[i] = fminf(key[2 * i], key[2 * i + 1]);
+                m2[i] = fmaxf(key[2 * i], key[2 * i + 1]);
+            }
 #pragma unroll
-                    for (int t = 0; t < 4; ++t) {
-                        const int j = j4 * 4 + t;
-                        const float dot = __uint_as_float(hi[j]) + __uint_as_float(lo[j]);
-                        const float dj = fmaf(-2.f, dot, cc[t] + xn);  // padded columns: FLT_MAX
-                        key[j] = __uint_as_float((__float_as_uint(dj) & ~31u) | (uint32_t)j);
-                    }
-                }
-                // the three smallest keys by a tournament of sorted lists (independent operations, short
-                // dependency chains): pairs -> triples -> ... ; the third smallest of two sorted triples is
-                // min(a3, b3, max(a1,b2), max(a2,b1))
-                float m1[16], m2[16], m3[8];
+            for (int i = 0; i < 8; ++i) {  // two sorted pairs -> sorted triple
+                const float a1 = m1[2 * i], a2 = m2[2 * i], b1 = m1[2 * i + 1], b2 = m2[2 * i + 1];
+                m1[i] = fminf(a1, b1);
+                m2[i] = fminf(fmaxf(a1, b1), fminf(a2, b2));
+                m3[i] = fminf(fmaxf(a1, b2), fmaxf(a2, b1));
+            }
 #pragma unroll
-                for (int i = 0; i < 16; ++i) {
-                    m1[i] = fminf(key[2 * i], key[2 * i + 1]);
-                    m2[i] = fmaxf(key[2 * i], key[2 * i + 1]);
-                }
+            for (int nn = 8; nn > 1; nn >>= 1) {
 #pragma unroll
-                for (int i = 0; i < 8; ++i) {  // two sorted pairs -> sorted triple
-                    const float a1 = m1[2 * i], a2 = m2[2 * i], b1 = m1[2 * i + 1], b2 = m2[2 * i + 1];
+                for (int i = 0; i < nn / 2; ++i) {
+                    const float a1 = m1[2 * i], a2 = m2[2 * i], a3 = m3[2 * i];
+                    const float b1 = m1[2 * i + 1], b2 = m2[2 * i + 1], b3 = m3[2 * i + 1];
                     m1[i] = fminf(a1, b1);
                     m2[i] = fminf(fmaxf(a1, b1), fminf(a2, b2));
-                    m3[i] = fminf(fmaxf(a1, b2), fmaxf(a2, b1));
+                    m3[i] = fminf(fminf(a3, b3), fminf(fmaxf(a1, b2), fmaxf(a2, b1)));
                 }
-#pragma unroll
-                for (int nn = 8; nn > 1; nn >>= 1) {
-#pragma unroll
-                    for (int i = 0; i < nn / 2; ++i) {
-                        const float a1 = m1[2 * i], a2 = m2[2 * i], a3 = m3[2 * i];
-                        const float b1 = m1[2 * i + 1], b2 = m2[2 * i + 1], b3 = m3[2 * i + 1];
-                        m1[i] = fminf(a1, b1);
-                        m2[i] = fminf(fmaxf(a1, b1), fminf(a2, b2));
-                        m3[i] = fminf(fminf(a3, b3), fminf(fmaxf(a1, b2), fmaxf(a2, b1)));
-                    }
-                }
-                const float b1 = m1[0], b2 = m2[0], b3 = m3[0];
-                const int i1 = (int)(__float_as_uint(b1) & 31u), i2 = (int)(__float_as_uint(b2) & 31u);
-                label = i1;
-                // safety test (see the file header); every quantity is an upper bound
-                const float scale = xn + cmax;
-                const float t = p.tol_x * sqrtf(xl);  // >= ||x - x^||
-                const float eps = p.eps_rel * scale + 7.63e-6f * (fabsf(b1) + fabsf(b2));
-                const float r1 = sqrtf(fmaxf(b1, 0.f) + p.abs_rel * scale);
-                const float safe = 4.f * t * r1 + eps;
-                const float margin = b2 - b1;
-                // runner-up: the pair bound.  Any other centroid j can truly beat c_1 only if ||c_1 - c_j|| <= 2 r_1:
-                // impossible when even the nearest such centroid is farther than that; otherwise the third best
-                // margin has to exceed `safe`.
-                const bool pair_ok = margin >= fminf(2.f * t * pd_s[i1 * 32 + i2] + eps, safe);
-                const float others = (__float_as_int(pd_s[32 * 32 + 64 + i1]) == i2) ? pd_s[32 * 32 + 32 + i1] : pd_s[32 * 32 + i1];
-                const bool third = valid && p.k > 2 && others <= 2.f * r1 &&
-                                   (b3 - b1) < safe + 7.63e-6f * fabsf(b3);  // a third candidate cannot be excluded
-                const bool amb = (valid && p.k > 1 && !pair_ok) || third;
-                verdict = (unsigned)i1 | ((unsigned)i2 << 8) | (amb ? kInfoUnsafe | (third ? kInfoReach : kInfoPair) : 0u);
-            } else {
-                // ---- general k: 16 scores at a time, running (best, second, argmin), loose bound ----
-                float b1 = FLT_MAX, b2 = FLT_MAX;
-                int i1 = 0;
-                for (int c0 = 0; c0 < p.k; c0 += 16) {
-                    uint32_t r[16], r2[16];
-                    tmem_ld16(taddr + c0, r);
-                    if (stacked) tmem_ld16(taddr + p.k_pad + c0, r2);
-                    tmem_wait_ld();
-#pragma unroll
-                    for (int j = 0; j < 16; ++j) {
-                        float dot = __uint_as_float(r[j]);
-                        if (stacked) dot += __uint_as_float(r2[j]);
-                        const float sc = fmaf(-2.f, dot, cn_s[c0 + j]);  // padded columns: FLT_MAX
-                        if (sc < b1) {
-                            b2 = b1;
-                            b1 = sc;
-                            i1 = c0 + j;
-                        } else {
-                            b2 = fminf(b2, sc);
-                        }
-                    }
-                }
-                if (p.xn_compute) {
-                    mbar_wait(xn_full0 + 8u * s, (uint32_t)((it / S) & 1));
-                    xn = xn_s[s * kTileM + row];
-                }
-                label = i1;
-                // 2|x||c| <= |x|^2 + |c|^2: the pair bound with ||c_a - c_b|| <= 2 max||c||
-                const float band = (2.f * p.abs_rel + p.eps_rel) * (xn + cmax);
-                const bool amb = valid && p.k > 1 && (b2 - b1) < band;
-                verdict = ((unsigned)i1 & 255u) | (amb ? kInfoUnsafe | kInfoAll : 0u);
-                tc_fence_before();
-                __syncwarp();
-                if (lane == 0) mbar_arrive(d_empty0 + 8u * db);
             }
+            const float b1 = m1[0], b2 = m2[0], b3 = m3[0];
+            const int i1 = (int)(__float_as_uint(b1) & 31u), i2 = (int)(__float_as_uint(b2) & 31u);
+            label = i1;
+            // safety test (see the file header); every quantity is an upper bound
+            const float scale = xn + cmax;
+            const float t = p.tol_x * sqrtf(xl);  // >= ||x - x^||
+            const float eps = p.eps_rel * scale + 7.63e-6f * (fabsf(b1) + fabsf(b2));
+            const float r1 = sqrtf(fmaxf(b1, 0.f) + p.abs_rel * scale);
+            const float safe = 4.f * t * r1 + eps;
+            const float margin = b2 - b1;
+            // runner-up: the pair bound.  Any other centroid j can truly beat c_1 only if ||c_1 - c_j|| <= 2 r_1:
+            // impossible when even the nearest such centroid is farther than that; otherwise the third best
+            // margin has to exceed `safe`.
+            const bool pair_ok = margin >= fminf(2.f * t * pd_s[i1 * 32 + i2] + eps, safe);
+            const float others = (__float_as_int(pd_s[32 * 32 + 64 + i1]) == i2) ? pd_s[32 * 32 + 32 + i1] : pd_s[32 * 32 + i1];
+            const bool third = valid && p.k > 2 && others <= 2.f * r1 &&
+                               (b3 - b1) < safe + 7.63e-6f * fabsf(b3);  // a third candidate cannot be excluded
+            const bool amb = (valid && p.k > 1 && !pair_ok) || third;
+            verdict = (unsigned)i1 | ((unsigned)i2 << 8) | (amb ? kInfoUnsafe | (third ? kInfoReach : kInfoPair) : 0u);
 
             // the verdict goes out with the row; unsafe rows keep the computed best as a provisional label (also in
             // the sums) until screen_fixup_kernel has decided them exactly
@@ -724,48 +680,21 @@ __global__ void __launch_bounds__(kThreads, 1)
                 if (rank_w == 0) hist[q][bin] = (uint8_t)__popc(peers);
                 named_bar_sync(bar_id, 128);
                 int pos, first;
-                if (bins <= 32) {
-                    // lane = bin
-                    const int h0 = hist[0][lane], h1 = hist[1][lane], h2 = hist[2][lane], h3 = hist[3][lane];
-                    const int tot = (lane < bins) ? h0 + h1 + h2 + h3 : 0;
-                    int incl = tot;
+                // lane = bin
+                const int h0 = hist[0][lane], h1 = hist[1][lane], h2 = hist[2][lane], h3 = hist[3][lane];
+                const int tot = (lane < bins) ? h0 + h1 + h2 + h3 : 0;
+                int incl = tot;
 #pragma unroll
-                    for (int o = 1; o < 32; o <<= 1) {
-                        const int v = __shfl_up_sync(0xffffffffu, incl, o);
-                        if (lane >= o) incl += v;
-                    }
-                    const int excl = incl - tot;
-                    const int mine = excl + (q > 0 ? h0 : 0) + (q > 1 ? h1 : 0) + (q > 2 ? h2 : 0);
-                    if (q == 0) s_base[sb][lane] = (unsigned short)excl;  // lanes >= bins hold the total (128)
-                    if (q == 0 && lane == 31) s_base[sb][32] = (unsigned short)incl;
-                    pos = __shfl_sync(0xffffffffu, mine, bin) + rank_w;
-                    first = pos == __shfl_sync(0xffffffffu, excl, bin);
-                } else {
-                    // lane owns `per` consecutive bins
-                    const int per = (bins + 31) >> 5;
-                    const int b0 = lane * per;
-                    int lane_total = 0;
-                    for (int bb = b0; bb < b0 + per && bb < bins; ++bb)
-                        lane_total += hist[0][bb] + hist[1][bb] + hist[2][bb] + hist[3][bb];
-                    int incl = lane_total;
-#pragma unroll
-                    for (int o = 1; o < 32; o <<= 1) {
-                        const int v = __shfl_up_sync(0xffffffffu, incl, o);
-                        if (lane >= o) incl += v;
-                    }
-                    int run = incl - lane_total;
-                    for (int bb = b0; bb < b0 + per && bb < bins; ++bb) {
-                        const int h0 = hist[0][bb], h1 = hist[1][bb], h2 = hist[2][bb], h3 = hist[3][bb];
-                        if (q == 0) s_base[sb][bb] = (unsigned short)run;
-                        s_off[g][q][bb] = (unsigned short)(run + (q > 0 ? h0 : 0) + (q > 1 ? h1 : 0) + (q > 2 ? h2 : 0));
-                        run += h0 + h1 + h2 + h3;
-                    }
-                    if (q == 0 && lane == 31) s_base[sb][bins] = (unsigned short)run;
-                    __syncwarp();
-                    const int start = s_off[g][q][bin];
-                    pos = start + rank_w;
-                    first = rank_w == 0 && hist[0][bin] * (q > 0) + hist[1][bin] * (q > 1) + hist[2][bin] * (q > 2) == 0;
+                for (int o = 1; o < 32; o <<= 1) {
+                    const int v = __shfl_up_sync(0xffffffffu, incl, o);
+                    if (lane >= o) incl += v;
                 }
+                const int excl = incl - tot;
+                const int mine = excl + (q > 0 ? h0 : 0) + (q > 1 ? h1 : 0) + (q > 2 ? h2 : 0);
+                if (q == 0) s_base[sb][lane] = (unsigned short)excl;  // lanes >= bins hold the total (128)
+                if (q == 0 && lane == 31) s_base[sb][32] = (unsigned short)incl;
+                pos = __shfl_sync(0xffffffffu, mine, bin) + rank_w;
+                first = pos == __shfl_sync(0xffffffffu, excl, bin);
                 {
                     // sorted position -> row offset inside an atom (r*pitch | swizzle bits), a first-of-run flag
                     // (bit 16) and the label (bits 17+)
@@ -802,137 +731,84 @@ __global__ void __launch_bounds__(kThreads, 1)
         const int ut = threadIdx.x - kUpdateWarp0 * 32;
         double* sacc = (double*)(smem + p.off_acc);
         const int nchunks = p.d >> 2;
-        const int l_lo = (u * p.k) >> 3, l_hi = ((u + 1) * p.k) >> 3;
-        const bool reg_path = p.k <= 32 && nchunks <= 32;
-        if (reg_path) {
-            // k <= 32: at most 4 owned labels.  Their FP32 sums live in registers (two packed pairs per
-            // label, added with FADD2) and are folded into the float64 shared accumulators every 8 tiles.
-            // Rows come in batches of 8 with predicated adds: a lone warp pays ~20 cycles per taken branch.
-            int lab[4];  // owned labels (-1 = free slot): balanced by cluster size, see IterState::own
+        // k <= 32: at most 4 owned labels.  Their FP32 sums live in registers (two packed pairs per
+        // label, added with FADD2) and are folded into the float64 shared accumulators every 8 tiles.
+        // Rows come in batches of 8 with predicated adds: a lone warp pays ~20 cycles per taken branch.
+        int lab[4];  // owned labels (-1 = free slot): balanced by cluster size, see IterState::own
 #pragma unroll
-            for (int li = 0; li < 4; ++li) lab[li] = p.st->own[u * 4 + li];
-            const bool active = lane < nchunks;
-            const int ch = active ? lane : 0;
-            const int a = ch >> 3;
-            const bool tail = a >= p.n_full;
-            const int col_off = (tail ? p.n_full : a) * kAtomBytes;
-            const int c16 = (tail ? (ch - p.n_full * 8) : (ch & 7)) << 4;
-            unsigned long long acc[4][2];
-            int cnt[4];
+        for (int li = 0; li < 4; ++li) lab[li] = p.st->own[u * 4 + li];
+        const bool active = lane < nchunks;
+        const int ch = active ? lane : 0;
+        const int a = ch >> 3;
+        const bool tail = a >= p.n_full;
+        const int col_off = (tail ? p.n_full : a) * kAtomBytes;
+        const int c16 = (tail ? (ch - p.n_full * 8) : (ch & 7)) << 4;
+        unsigned long long acc[4][2];
+        int cnt[4];
+#pragma unroll
+        for (int li = 0; li < 4; ++li) {
+            acc[li][0] = acc[li][1] = 0ull;
+            cnt[li] = 0;
+        }
+        auto fold = [&]() {
 #pragma unroll
             for (int li = 0; li < 4; ++li) {
-                acc[li][0] = acc[li][1] = 0ull;
-                cnt[li] = 0;
-            }
-            auto fold = [&]() {
-#pragma unroll
-                for (int li = 0; li < 4; ++li) {
-                    if (lab[li] >= 0) {
-                        if (active) {
-                            double2* dst = reinterpret_cast<double2*>(sacc + (size_t)lab[li] * p.d + ch * 4);
-                            const float2 lo = unpack2(acc[li][0]), hi = unpack2(acc[li][1]);
-                            double2 a0 = dst[0], a1 = dst[1];
-                            a0.x += (double)lo.x;
-                            a0.y += (double)lo.y;
-                            a1.x += (double)hi.x;
-                            a1.y += (double)hi.y;
-                            dst[0] = a0;
-                            dst[1] = a1;
-                        }
-                        if (lane == 0) sacc[p.k * p.d + lab[li]] += (double)cnt[li];
-                        acc[li][0] = acc[li][1] = 0ull;
-                        cnt[li] = 0;
+                if (lab[li] >= 0) {
+                    if (active) {
+                        double2* dst = reinterpret_cast<double2*>(sacc + (size_t)lab[li] * p.d + ch * 4);
+                        const float2 lo = unpack2(acc[li][0]), hi = unpack2(acc[li][1]);
+                        double2 a0 = dst[0], a1 = dst[1];
+                        a0.x += (double)lo.x;
+                        a0.y += (double)lo.y;
+                        a1.x += (double)hi.x;
+                        a1.y += (double)hi.y;
+                        dst[0] = a0;
+                        dst[1] = a1;
                     }
+                    if (lane == 0) sacc[p.k * p.d + lab[li]] += (double)cnt[li];
+                    acc[li][0] = acc[li][1] = 0ull;
+                    cnt[li] = 0;
                 }
-            };
-            int64_t it = 0;
-            for (int64_t tile = first_tile; tile < p.num_tiles; tile += tile_step, ++it) {
-                const int s = (int)(it % S);
-                const int sb = (int)(it & 1);
-                mbar_wait(s_full0 + 8u * sb, (uint32_t)((it >> 1) & 1));
-                mbar_wait(x_full0 + 8u * s, (uint32_t)((it / S) & 1));
-                if (ut == 0) trace_ev(p, it, 7);
-                const uint8_t* colp = smem + (size_t)s * stage_bytes + col_off;
-                // low halves of the perm words = byte offsets inside the atom
-                const unsigned short* perm = reinterpret_cast<const unsigned short*>(tail ? s_permT[sb] : s_perm[sb]);
+            }
+        };
+        int64_t it = 0;
+        for (int64_t tile = first_tile; tile < p.num_tiles; tile += tile_step, ++it) {
+            const int s = (int)(it % S);
+            const int sb = (int)(it & 1);
+            mbar_wait(s_full0 + 8u * sb, (uint32_t)((it >> 1) & 1));
+            mbar_wait(x_full0 + 8u * s, (uint32_t)((it / S) & 1));
+            if (ut == 0) trace_ev(p, it, 7);
+            const uint8_t* colp = smem + (size_t)s * stage_bytes + col_off;
+            // low halves of the perm words = byte offsets inside the atom
+            const unsigned short* perm = reinterpret_cast<const unsigned short*>(tail ? s_permT[sb] : s_perm[sb]);
 #pragma unroll
-                for (int li = 0; li < 4; ++li) {
-                    if (lab[li] >= 0) {
-                        const int beg = s_base[sb][lab[li]], end = s_base[sb][lab[li] + 1];
+            for (int li = 0; li < 4; ++li) {
+                if (lab[li] >= 0) {
+                    const int beg = s_base[sb][lab[li]], end = s_base[sb][lab[li] + 1];
 #pragma unroll 1
-                        for (int base = beg; base < end; base += 8) {
-                            unsigned int w[8];
-                            ulonglong2 v[8];
+                    for (int base = beg; base < end; base += 8) {
+                        unsigned int w[8];
+                        ulonglong2 v[8];
 #pragma unroll
-                            for (int j = 0; j < 8; ++j) w[j] = perm[2 * (base + j)];  // past `end`: stale but valid offsets
+                        for (int j = 0; j < 8; ++j) w[j] = perm[2 * (base + j)];  // past `end`: stale but valid offsets
 #pragma unroll
-                            for (int j = 0; j < 8; ++j) v[j] = *reinterpret_cast<const ulonglong2*>(colp + (w[j] ^ c16));
+                        for (int j = 0; j < 8; ++j) v[j] = *reinterpret_cast<const ulonglong2*>(colp + (w[j] ^ c16));
 #pragma unroll
-                            for (int j = 0; j < 8; ++j) {
-                                add2_if(acc[li][0], v[j].x, base + j, end);
-                                add2_if(acc[li][1], v[j].y, base + j, end);
-                            }
-                        }
-                        cnt[li] += end - beg;
-                    }
-                }
-                __syncwarp();
-                if (lane == 0) {
-                    mbar_arrive(s_empty0 + 8u * sb);
-                    mbar_arrive(x_empty0 + 8u * s);
-                }
-                if (lane == 0) trace_ev(p, it, 8 + u);
-                if ((it & 7) == 7 || tile + tile_step >= p.num_tiles) fold();  // single (rare) fold site
-            }
-        } else {
-            // general shapes: flat walk over the owned range, run sums flushed when the next run opens
-            int64_t it = 0;
-            for (int64_t tile = first_tile; tile < p.num_tiles; tile += tile_step, ++it) {
-                const int s = (int)(it % S);
-                const int sb = (int)(it & 1);
-                mbar_wait(s_full0 + 8u * sb, (uint32_t)((it >> 1) & 1));
-                mbar_wait(x_full0 + 8u * s, (uint32_t)((it / S) & 1));
-                const uint8_t* stage = smem + (size_t)s * stage_bytes;
-                const int pb = s_base[sb][l_lo], pe = s_base[sb][l_hi];
-                for (int ch = lane; ch < nchunks; ch += 32) {
-                    const int a = ch >> 3;
-                    const bool tail = a >= p.n_full;
-                    const uint8_t* colp = stage + (tail ? p.n_full : a) * kAtomBytes;
-                    const int c16 = (tail ? (ch - p.n_full * 8) : (ch & 7)) << 4;
-                    const int* perm = tail ? s_permT[sb] : s_perm[sb];
-                    float4 r = make_float4(0.f, 0.f, 0.f, 0.f);
-                    int cur = -1;
-                    for (int pos = pb; pos <= pe; ++pos) {
-                        const int w = pos < pe ? perm[pos] : (1 << 16);
-                        if ((w & (1 << 16)) && cur >= 0) {  // a new run opens (or the range ends): flush (warp-uniform)
-                            double2* dst = reinterpret_cast<double2*>(sacc + (size_t)cur * p.d + ch * 4);
-                            double2 a0 = dst[0], a1 = dst[1];
-                            a0.x += (double)r.x;
-                            a0.y += (double)r.y;
-                            a1.x += (double)r.z;
-                            a1.y += (double)r.w;
-                            dst[0] = a0;
-                            dst[1] = a1;
-                            r = make_float4(0.f, 0.f, 0.f, 0.f);
-                        }
-                        if (pos < pe) {
-                            cur = w >> 17;
-                            const float4 v = *reinterpret_cast<const float4*>(colp + ((w & 0xFFFF) ^ c16));
-                            r.x += v.x;
-                            r.y += v.y;
-                            r.z += v.z;
-                            r.w += v.w;
+                        for (int j = 0; j < 8; ++j) {
+                            add2_if(acc[li][0], v[j].x, base + j, end);
+                            add2_if(acc[li][1], v[j].y, base + j, end);
                         }
                     }
-                }
-                for (int l = l_lo + lane; l < l_hi; l += 32)
-                    sacc[p.k * p.d + l] += (double)(s_base[sb][l + 1] - s_base[sb][l]);
-                __syncwarp();
-                if (lane == 0) {
-                    mbar_arrive(s_empty0 + 8u * sb);
-                    mbar_arrive(x_empty0 + 8u * s);
+                    cnt[li] += end - beg;
                 }
             }
+            __syncwarp();
+            if (lane == 0) {
+                mbar_arrive(s_empty0 + 8u * sb);
+                mbar_arrive(x_empty0 + 8u * s);
+            }
+            if (lane == 0) trace_ev(p, it, 8 + u);
+            if ((it & 7) == 7 || tile + tile_step >= p.num_tiles) fold();  // single (rare) fold site
         }
         named_bar_sync(3, 256);
         const int acc_n = p.k * p.d + p.k;
@@ -951,7 +827,7 @@ __global__ void __launch_bounds__(kThreads, 1)
 }
 
 // ---- host side ---------------------------------------------------------------------------------
-constexpr int kStaticSmem = 9 * 1024;  // upper bound of the kernel's static shared arrays
+constexpr int kStaticSmem = 4 * 1024;  // upper bound of the kernel's static shared arrays
 
 struct Plan {
     int k_pad, n_full, tail_cols, d_pad, num_stages, num_d, stage_bytes;
@@ -963,7 +839,8 @@ Plan make_plan(int d, int k, bool with_acc) {
     Plan pl = {};
     pl.ok = false;
     if (d <= 0 || k <= 0 || d > kMaxD || k > kMaxK || (d & 3)) return pl;
-    pl.k_pad = k <= 32 ? 32 : (k + 15) & ~15;  // k <= 32: the register-resident assign path wants 32 columns
+    if (with_acc && d > 128) return pl;  // the update warps map one float4 column chunk to a lane
+    pl.k_pad = 32;  // the assign warps hold one row's 32 scores in registers
     // K-atoms: 32-float SWIZZLE_128B atoms, and a narrow SWIZZLE_32B / 64B tail when d % 32 is in 4..16
     const int rem = d & 31;
     pl.n_full = d >> 5;
@@ -972,11 +849,10 @@ Plan make_plan(int d, int k, bool with_acc) {
     else if (rem > 8) pl.tail_cols = 16;
     else if (rem > 0) pl.tail_cols = 8;
     pl.d_pad = pl.n_full * 32 + pl.tail_cols;
-    const int dcols = pl.k_pad <= 128 ? 2 * pl.k_pad : pl.k_pad;
-    pl.num_d = dcols <= 128 ? 4 : 2;  // score buffers of dcols TMEM columns each (512 columns in all)
+    pl.num_d = 4;  // score buffers of 2*k_pad = 64 TMEM columns each
     pl.stage_bytes = pl.n_full * kAtomBytes + kTileM * pl.tail_cols * 4;
     const int c_bytes = 2 * pl.k_pad * pl.d_pad * 4;
-    const int pd_bytes = k <= 32 ? (32 * 32 + 3 * 32) * 4 : 0;  // pair distances + per-centroid neighbour data
+    const int pd_bytes = (32 * 32 + 3 * 32) * 4;  // pair distances + per-centroid neighbour data
     const int acc_bytes = with_acc ? (int)((sizeof(double) * ((size_t)k * d + k) + 15) & ~(size_t)15) : 0;
     const int fixed = c_bytes + pd_bytes + acc_bytes + pl.k_pad * 4 + 2 * kMaxStages * kTileM * 4 + 256 /*barriers*/ + 1024 /*align*/ +
                       kStaticSmem;
