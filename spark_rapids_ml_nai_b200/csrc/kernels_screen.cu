@@ -70,7 +70,7 @@ constexpr int kHist = 40;  // label bins (k + 1) rounded up
 constexpr unsigned int kInfoUnsafe = 1u << 31;
 constexpr unsigned int kInfoPair = 0u << 16;   // exactly the best and the runner-up
 constexpr unsigned int kInfoReach = 1u << 16;  // every centroid within 2 r_1 of the computed best
-constexpr unsigned int kInfoAll = 2u << 16;    // every centroid
+[[maybe_unused]] constexpr unsigned int kInfoAll = 2u << 16;  // every centroid (kept for producers without a reach)
 
 struct ScParams {
     int64_t n;

@@ -1,4 +1,4 @@
-"""One traced lloyd_step on C2-like blobs with the true centres (development aid; needs a B200KM_ENABLE_TRACE build)."""
+"""A traced 3-iteration fit on C2-like blobs from the true centres (or, with a 2nd argument, random rows) (development aid; needs a B200KM_ENABLE_TRACE build)."""
 import sys, os
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
@@ -12,5 +12,5 @@ X = torch.randn((n, d), generator=g, device=dev) + centers[lab]
 h = _native.Handle(0)
 h.set_path(int(sys.argv[1]) if len(sys.argv) > 1 else _native.PATH_TC)
 C = centers.contiguous() if len(sys.argv) < 3 else X[torch.randperm(n, generator=g, device=dev)[:k]].clone()
-h.lloyd_step(X, C)
+h.fit(X, C, max_iter=3, tol=0.0, want_inertia=False)  # the trace file holds the last pass (row norms read back)
 torch.cuda.synchronize()
