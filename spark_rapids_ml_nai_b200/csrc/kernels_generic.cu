@@ -496,31 +496,42 @@ __global__ void __launch_bounds__(128) finalize_kernel(float* __restrict__ C, in
             st->n_iter += 1;
             acc[(size_t)k * d + k] = 0.0;
             if (shift2 < tol) st->done = 1;
-            if (k <= 32) {
-                // update-warp ownership for the next pass: largest cluster first onto the least loaded warp
-                // with a free slot (the per-tile update time follows the rows a warp owns)
+        }
+        if (k <= 32) {
+            // update-warp ownership for the next pass: largest cluster first onto the least loaded warp with a
+            // free slot (the per-tile update time follows the rows a warp owns).  Lane = cluster: the largest
+            // remaining one by a warp max, the assignment by lane 0; everything stays in registers / shared.
+            __shared__ signed char s_own[32];
+            if (threadIdx.x < 32) {
+                const int lane = threadIdx.x;
+                s_own[lane] = (signed char)-1;
+                double mine = lane < k ? ((volatile double*)cnt_part)[lane] : -1.0;
                 double load[8] = {0, 0, 0, 0, 0, 0, 0, 0};
                 int used[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-                unsigned int taken = 0;
-                for (int q = 0; q < 32; ++q) st->own[q] = (signed char)-1;
                 for (int r = 0; r < k; ++r) {
-                    int best = -1;
-                    double bc = -1.0;
-                    for (int q = 0; q < k; ++q) {
-                        const double c = ((volatile double*)cnt_part)[q];
-                        if (!((taken >> q) & 1u) && c > bc) {
-                            bc = c;
-                            best = q;
+                    // arg max over the lanes, ties to the lowest cluster index
+                    double bc = mine;
+                    int best = lane;
+#pragma unroll
+                    for (int o = 16; o > 0; o >>= 1) {
+                        const double oc = __shfl_xor_sync(0xffffffffu, bc, o);
+                        const int ob = __shfl_xor_sync(0xffffffffu, best, o);
+                        if (oc > bc || (oc == bc && ob < best)) {
+                            bc = oc;
+                            best = ob;
                         }
                     }
-                    taken |= 1u << best;
+                    if (lane == best) mine = -1.0;
                     int w = -1;
+#pragma unroll
                     for (int u = 0; u < 8; ++u)
                         if (used[u] < 4 && (w < 0 || load[u] < load[w])) w = u;
-                    st->own[w * 4 + used[w]] = (signed char)best;
+                    if (lane == 0) s_own[w * 4 + used[w]] = (signed char)best;
                     used[w] += 1;
                     load[w] += bc;
                 }
+                __syncwarp();
+                st->own[lane] = s_own[lane];
             }
         }
     }
