@@ -819,6 +819,13 @@ __global__ void __launch_bounds__(kThreads, 1)
         }
     }
 
+#ifdef B200KM_ENABLE_TRACE
+    if (p.trace && threadIdx.x == 0) {  // per-CTA finish time (ns), slots past the per-tile events of CTA 0
+        unsigned long long t;
+        asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+        p.trace[3900 + blockIdx.x] = t;
+    }
+#endif
     tc_fence_before();
     __syncthreads();
     if (warp == 1) {
