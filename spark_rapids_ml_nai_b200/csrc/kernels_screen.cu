@@ -61,7 +61,8 @@ constexpr int kMaxSmem = 227 * 1024;
 constexpr int kMaxStages = 4;
 constexpr int kMaxND = 4;
 constexpr int kMaxD = 256;
-constexpr int kMaxK = 32;  // the scores of a row live in registers; larger k runs the split-TF32 kernel
+constexpr int kMaxK = 128;    // labels-only passes; larger k runs the split-TF32 kernel
+constexpr int kMaxKAcc = 32;  // passes with the update stage (register accumulators, lane = label in the sort)
 constexpr int kHist = 40;  // label bins (k + 1) rounded up
 
 // Per-row verdict written by the screen kernel: bits 0-7 the computed best centroid (the row's provisional
@@ -198,6 +199,38 @@ __global__ void __launch_bounds__(256) screen_inertia_fix_kernel(const float* __
         const double v = acc[kd + k] + s;
         acc[kd + k] = v > 0.0 ? v : 0.0;
     }
+}
+
+// The three smallest of 32 keys by a tournament of sorted lists (independent operations, short dependency
+// chains): pairs -> triples -> ...; the third smallest of two sorted triples is min(a3, b3, max(a1,b2), max(a2,b1)).
+__device__ __forceinline__ void top3_of_32(const float (&key)[32], float& o1, float& o2, float& o3) {
+    float m1[16], m2[16], m3[8];
+#pragma unroll
+    for (int i = 0; i < 16; ++i) {
+        m1[i] = fminf(key[2 * i], key[2 * i + 1]);
+        m2[i] = fmaxf(key[2 * i], key[2 * i + 1]);
+    }
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {  // two sorted pairs -> sorted triple
+        const float a1 = m1[2 * i], a2 = m2[2 * i], b1 = m1[2 * i + 1], b2 = m2[2 * i + 1];
+        m1[i] = fminf(a1, b1);
+        m2[i] = fminf(fmaxf(a1, b1), fminf(a2, b2));
+        m3[i] = fminf(fmaxf(a1, b2), fmaxf(a2, b1));
+    }
+#pragma unroll
+    for (int nn = 8; nn > 1; nn >>= 1) {
+#pragma unroll
+        for (int i = 0; i < nn / 2; ++i) {
+            const float a1 = m1[2 * i], a2 = m2[2 * i], a3 = m3[2 * i];
+            const float b1 = m1[2 * i + 1], b2 = m2[2 * i + 1], b3 = m3[2 * i + 1];
+            m1[i] = fminf(a1, b1);
+            m2[i] = fminf(fmaxf(a1, b1), fminf(a2, b2));
+            m3[i] = fminf(fminf(a3, b3), fminf(fmaxf(a1, b2), fmaxf(a2, b1)));
+        }
+    }
+    o1 = m1[0];
+    o2 = m2[0];
+    o3 = m3[0];
 }
 
 // Exact decision of the rows the screen left open (bit 31 of their info word), straight from HBM: one warp per
@@ -359,7 +392,8 @@ __global__ void __launch_bounds__(kThreads, 1)
     const int ND = p.num_d;  // power of two
     const int stage_bytes = p.stage_bytes;
     const int c_block = 2 * p.k_pad * 128;  // bytes of one full-atom block [c_hi rows | c_lo rows]
-    const int dcols = 2 * p.k_pad;  // TMEM columns of one score buffer: c_hi products | c_lo products
+    const int dcols = p.k_pad;  // TMEM columns of one score buffer (the c_hi and c_lo products add up in place)
+    const int n_groups = p.acc ? 2 : 4;  // assign groups: without an update stage its warps score tiles too
 
     // barrier table
     const uint32_t bar0 = smem_base + p.off_bar;
@@ -419,10 +453,10 @@ __global__ void __launch_bounds__(kThreads, 1)
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
-    if (p.k <= 32) {
+    {
         // per centroid: its nearest other centroid and the distances to the nearest and the second nearest one
         // (the third-candidate test of the assign warps); written before any consumer can have a tile
-        if (threadIdx.x < 32) {
+        if (threadIdx.x < p.k) {
             const float* pd_init = (const float*)(smem + p.off_pd);
             float* nb = (float*)(smem + p.off_pd) + 32 * 32;
             const int i = threadIdx.x;
@@ -430,7 +464,7 @@ __global__ void __launch_bounds__(kThreads, 1)
             int n1 = -1;
             for (int j = 0; j < p.k; ++j) {
                 if (j == i) continue;
-                const float v = pd_init[i * 32 + j];
+                const float v = p.k <= 32 ? pd_init[i * 32 + j] : __ldg(p.pd + (size_t)i * p.k + j);
                 if (v < d1) {
                     d2 = d1;
                     d1 = v;
@@ -440,12 +474,11 @@ __global__ void __launch_bounds__(kThreads, 1)
                 }
             }
             nb[i] = d1;
-            nb[32 + i] = d2;
-            nb[64 + i] = __int_as_float(n1);
+            nb[kMaxK + i] = d2;
+            nb[2 * kMaxK + i] = __int_as_float(n1);
         }
         __syncthreads();
     }
-
     const int64_t first_tile = blockIdx.x;
     const int64_t tile_step = gridDim.x;
 
@@ -482,8 +515,8 @@ __global__ void __launch_bounds__(kThreads, 1)
         // code costs ~100 cycles per instruction, ~40 from warp-uniform code: tools/mma_bench.cu).  Both
         // operands come from shared memory: A = the X tile exactly as TMA wrote it (K-major, swizzled), B =
         // the TF32 centroids; consecutive K-steps differ only in the descriptors' start address (+32 B).
-        // B is the stacked block [c_hi ; c_lo] (N = 2*k_pad, one instruction per K-step; the assign warps add
-        // the two halves).
+        // B holds [c_hi rows ; c_lo rows] per K-atom; a K-step is two instructions into the same k_pad columns:
+        // x^.c_hi and x^.c_lo.
         const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(kTileM >> 4) << 24) |
                                ((uint32_t)(dcols >> 3) << 17);
         const int tail_row_bytes = p.tail_cols ? p.tail_cols * 4 : 128;
@@ -491,6 +524,8 @@ __global__ void __launch_bounds__(kThreads, 1)
         const uint64_t bdesc_tail = make_b_desc(smem_base + p.off_c + p.n_full * c_block, tail_row_bytes);
         const uint64_t adesc_full = make_b_desc(smem_base, 128);
         const uint64_t adesc_tail = make_b_desc(smem_base + p.n_full * kAtomBytes, tail_row_bytes);
+        const uint64_t lo_full = (uint64_t)((p.k_pad * 128) >> 4);  // c_lo rows inside an atom block
+        const uint64_t lo_tail = (uint64_t)((p.k_pad * tail_row_bytes) >> 4);
         const int tail_steps = p.tail_cols >> 3;
         mbar_wait(c_full, 0);
         int64_t it = 0;
@@ -510,6 +545,7 @@ __global__ void __launch_bounds__(kThreads, 1)
 #pragma unroll
                     for (int kk = 0; kk < 4; ++kk) {
                         mma_tf32_ss(d_tmem, ad + 2 * kk, bd + 2 * kk, idesc, (a | kk) != 0);
+                        mma_tf32_ss(d_tmem, ad + 2 * kk, bd + lo_full + 2 * kk, idesc, 1);
                     }
                     ad += (uint64_t)(kAtomBytes >> 4);
                     bd += (uint64_t)(c_block >> 4);
@@ -517,6 +553,7 @@ __global__ void __launch_bounds__(kThreads, 1)
 #pragma unroll 1
                 for (int kk = 0; kk < tail_steps; ++kk) {
                     mma_tf32_ss(d_tmem, adesc_tail + soff + 2 * kk, bdesc_tail + 2 * kk, idesc, (p.n_full | kk) != 0);
+                    mma_tf32_ss(d_tmem, adesc_tail + soff + 2 * kk, bdesc_tail + lo_tail + 2 * kk, idesc, 1);
                 }
                 tc_commit(d_full0 + 8u * db);
                 trace_ev(p, it, 2);
@@ -544,10 +581,11 @@ __global__ void __launch_bounds__(kThreads, 1)
                 if (lane == 0) mbar_arrive(xn_full0 + 8u * s);
             }
         }
-    } else if (warp >= kAssignWarp0 && warp < kUpdateWarp0) {
+    } else if (warp >= kAssignWarp0 && (warp < kUpdateWarp0 || !p.acc)) {
         // ======================================== assign ========================================
-        // Two groups of four warps take alternate tiles (group g owns the sort buffer of its parity), so the
-        // argmin / re-decision / sort latency of one tile overlaps the next tile's.
+        // Groups of four warps take tiles in turn (two groups when there is an update stage - group g then owns
+        // the sort buffer of its parity -, four when the update warps are free to score tiles too), so the
+        // top-3 / verdict / sort latency of one tile overlaps the next tiles'.
         const int g = (warp - kAssignWarp0) >> 2;
         const int q = warp & 3;  // = the warp's TMEM lane quarter
         const int row = q * 32 + lane;
@@ -556,11 +594,12 @@ __global__ void __launch_bounds__(kThreads, 1)
         float* cn_s = (float*)(smem + p.off_cn);
         float* xn_s = (float*)(smem + p.off_xn);
         const float cmax = p.st->cnorm_max;
-        const float* pd_s = (const float*)(smem + p.off_pd);
+        const float* pd_s = (const float*)(smem + p.off_pd);        // [32][32] pair distances (k <= 32)
+        const float* nb_s = pd_s + 32 * 32;                        // per centroid: nearest, second nearest, who
         const int sb = g;
 
         double sum_xn = 0.0;
-        for (int64_t it = g;; it += 2) {
+        for (int64_t it = g;; it += n_groups) {
             const int64_t tile = first_tile + it * tile_step;
             if (tile >= p.num_tiles) break;
             const int s = (int)(it % S);
@@ -579,79 +618,62 @@ __global__ void __launch_bounds__(kThreads, 1)
             const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(db * dcols);
             int label = 0;
             unsigned int verdict = 0;  // this row's info word
-            // ---- k_pad <= 32: all scores stay in registers ----
-            uint32_t hi[32], lo[32];
-            tmem_ld32(taddr, hi);
-            tmem_ld32(taddr + 32, lo);
-            tmem_wait_ld();
-            tc_fence_before();
-            __syncwarp();
-            if (lane == 0) mbar_arrive(d_empty0 + 8u * db);  // the score buffer is free again
+            // ---- 32 scores at a time into registers; keys D_j = ||x||^2 + ||c_j||^2 - 2 x^.c_j carry the centroid
+            // index in their 7 low mantissa bits (a perturbation below 2^-16 |D_j|, covered by the bound) ----
             if (p.xn_compute) {
                 mbar_wait(xn_full0 + 8u * s, (uint32_t)((it / S) & 1));
                 xn = xn_s[s * kTileM + row];
                 xl = xn_s[(kMaxStages + s) * kTileM + row];
             }
-            // keys: D_j = ||x||^2 + ||c_j||^2 - 2 x^.c_j with the centroid index in the 5 low mantissa bits
-            // (a perturbation below 2^-18 |D_j|, covered by the bound)
-            float key[32];
-            const float4* cn4 = reinterpret_cast<const float4*>(cn_s);
+            float b1 = FLT_MAX, b2 = FLT_MAX, b3 = FLT_MAX;
+#pragma unroll 1
+            for (int c0 = 0; c0 < p.k_pad; c0 += 32) {
+                uint32_t sc[32];
+                tmem_ld32(taddr + c0, sc);
+                tmem_wait_ld();
+                float key[32];
+                const float4* cn4 = reinterpret_cast<const float4*>(cn_s + c0);
 #pragma unroll
-            for (int j4 = 0; j4 < 8; ++j4) {
-                const float4 c = cn4[j4];
-                const float cc[4] = {c.x, c.y, c.z, c.w};
+                for (int j4 = 0; j4 < 8; ++j4) {
+                    const float4 c = cn4[j4];
+                    const float cc[4] = {c.x, c.y, c.z, c.w};
 #pragma unroll
-                for (int t = 0; t < 4; ++t) {
-                    const int j = j4 * 4 + t;
-                    const float dot = __uint_as_float(hi[j]) + __uint_as_float(lo[j]);
-                    const float dj = fmaf(-2.f, dot, cc[t] + xn);  // padded columns: FLT_MAX
-                    key[j] = __uint_as_float((__float_as_uint(dj) & ~31u) | (uint32_t)j);
+                    for (int t = 0; t < 4; ++t) {
+                        const int j = j4 * 4 + t;
+                        const float dj = fmaf(-2.f, __uint_as_float(sc[j]), cc[t] + xn);  // padded columns: FLT_MAX
+                        key[j] = __uint_as_float((__float_as_uint(dj) & ~127u) | (uint32_t)(c0 + j));
+                    }
                 }
+                float t1, t2, t3;
+                top3_of_32(key, t1, t2, t3);
+                // merge the chunk's sorted triple into the running one
+                const float n1 = fminf(b1, t1);
+                const float n2 = fminf(fmaxf(b1, t1), fminf(b2, t2));
+                const float n3 = fminf(fminf(b3, t3), fminf(fmaxf(b1, t2), fmaxf(b2, t1)));
+                b1 = n1;
+                b2 = n2;
+                b3 = n3;
             }
-            // the three smallest keys by a tournament of sorted lists (independent operations, short
-            // dependency chains): pairs -> triples -> ... ; the third smallest of two sorted triples is
-            // min(a3, b3, max(a1,b2), max(a2,b1))
-            float m1[16], m2[16], m3[8];
-#pragma unroll
-            for (int i = 0; i < 16; ++i) {
-                m1[i] = fminf(key[2 * i], key[2 * i + 1]);
-                m2[i] = fmaxf(key[2 * i], key[2 * i + 1]);
-            }
-#pragma unroll
-            for (int i = 0; i < 8; ++i) {  // two sorted pairs -> sorted triple
-                const float a1 = m1[2 * i], a2 = m2[2 * i], b1 = m1[2 * i + 1], b2 = m2[2 * i + 1];
-                m1[i] = fminf(a1, b1);
-                m2[i] = fminf(fmaxf(a1, b1), fminf(a2, b2));
-                m3[i] = fminf(fmaxf(a1, b2), fmaxf(a2, b1));
-            }
-#pragma unroll
-            for (int nn = 8; nn > 1; nn >>= 1) {
-#pragma unroll
-                for (int i = 0; i < nn / 2; ++i) {
-                    const float a1 = m1[2 * i], a2 = m2[2 * i], a3 = m3[2 * i];
-                    const float b1 = m1[2 * i + 1], b2 = m2[2 * i + 1], b3 = m3[2 * i + 1];
-                    m1[i] = fminf(a1, b1);
-                    m2[i] = fminf(fmaxf(a1, b1), fminf(a2, b2));
-                    m3[i] = fminf(fminf(a3, b3), fminf(fmaxf(a1, b2), fmaxf(a2, b1)));
-                }
-            }
-            const float b1 = m1[0], b2 = m2[0], b3 = m3[0];
-            const int i1 = (int)(__float_as_uint(b1) & 31u), i2 = (int)(__float_as_uint(b2) & 31u);
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(d_empty0 + 8u * db);  // the score buffer is free again
+            const int i1 = (int)(__float_as_uint(b1) & 127u), i2 = (int)(__float_as_uint(b2) & 127u);
             label = i1;
             // safety test (see the file header); every quantity is an upper bound
             const float scale = xn + cmax;
             const float t = p.tol_x * sqrtf(xl);  // >= ||x - x^||
-            const float eps = p.eps_rel * scale + 7.63e-6f * (fabsf(b1) + fabsf(b2));
+            const float eps = p.eps_rel * scale + 1.6e-5f * (fabsf(b1) + fabsf(b2));
             const float r1 = sqrtf(fmaxf(b1, 0.f) + p.abs_rel * scale);
             const float safe = 4.f * t * r1 + eps;
             const float margin = b2 - b1;
             // runner-up: the pair bound.  Any other centroid j can truly beat c_1 only if ||c_1 - c_j|| <= 2 r_1:
             // impossible when even the nearest such centroid is farther than that; otherwise the third best
             // margin has to exceed `safe`.
-            const bool pair_ok = margin >= fminf(2.f * t * pd_s[i1 * 32 + i2] + eps, safe);
-            const float others = (__float_as_int(pd_s[32 * 32 + 64 + i1]) == i2) ? pd_s[32 * 32 + 32 + i1] : pd_s[32 * 32 + i1];
+            const float pd12 = p.k <= 32 ? pd_s[i1 * 32 + i2] : __ldg(p.pd + (size_t)i1 * p.k + min(i2, p.k - 1));
+            const bool pair_ok = margin >= fminf(2.f * t * pd12 + eps, safe);
+            const float others = (__float_as_int(nb_s[2 * kMaxK + i1]) == i2) ? nb_s[kMaxK + i1] : nb_s[i1];
             const bool third = valid && p.k > 2 && others <= 2.f * r1 &&
-                               (b3 - b1) < safe + 7.63e-6f * fabsf(b3);  // a third candidate cannot be excluded
+                               (b3 - b1) < safe + 1.6e-5f * fabsf(b3);  // a third candidate cannot be excluded
             const bool amb = (valid && p.k > 1 && !pair_ok) || third;
             verdict = (unsigned)i1 | ((unsigned)i2 << 8) | (amb ? kInfoUnsafe | (third ? kInfoReach : kInfoPair) : 0u);
 
@@ -846,8 +868,8 @@ Plan make_plan(int d, int k, bool with_acc) {
     Plan pl = {};
     pl.ok = false;
     if (d <= 0 || k <= 0 || d > kMaxD || k > kMaxK || (d & 3)) return pl;
-    if (with_acc && d > 128) return pl;  // the update warps map one float4 column chunk to a lane
-    pl.k_pad = 32;  // the assign warps hold one row's 32 scores in registers
+    if (with_acc && (d > 128 || k > kMaxKAcc)) return pl;  // update warps: lane = float4 column chunk, <= 4 labels each
+    pl.k_pad = (k + 31) & ~31;  // the assign warps take the scores 32 at a time
     // K-atoms: 32-float SWIZZLE_128B atoms, and a narrow SWIZZLE_32B / 64B tail when d % 32 is in 4..16
     const int rem = d & 31;
     pl.n_full = d >> 5;
@@ -856,10 +878,10 @@ Plan make_plan(int d, int k, bool with_acc) {
     else if (rem > 8) pl.tail_cols = 16;
     else if (rem > 0) pl.tail_cols = 8;
     pl.d_pad = pl.n_full * 32 + pl.tail_cols;
-    pl.num_d = 4;  // score buffers of 2*k_pad = 64 TMEM columns each
+    pl.num_d = 4;  // score buffers of k_pad <= 128 TMEM columns each
     pl.stage_bytes = pl.n_full * kAtomBytes + kTileM * pl.tail_cols * 4;
     const int c_bytes = 2 * pl.k_pad * pl.d_pad * 4;
-    const int pd_bytes = (32 * 32 + 3 * 32) * 4;  // pair distances + per-centroid neighbour data
+    const int pd_bytes = (32 * 32 + 3 * kMaxK) * 4;  // pair distances (k <= 32) + per-centroid neighbour data
     const int acc_bytes = with_acc ? (int)((sizeof(double) * ((size_t)k * d + k) + 15) & ~(size_t)15) : 0;
     const int fixed = c_bytes + pd_bytes + acc_bytes + pl.k_pad * 4 + 2 * kMaxStages * kTileM * 4 + 256 /*barriers*/ + 1024 /*align*/ +
                       kStaticSmem;

@@ -88,6 +88,18 @@ def test_predict_labels_only_uses_the_screen_and_is_exact(handle):
     assert torch.equal(labels, labels2)
 
 
+@pytest.mark.parametrize("n,d,k", [(20000, 64, 100), (9000, 32, 128), (7000, 100, 33), (6000, 16, 65)])
+def test_labels_only_predict_up_to_128_centroids_runs_the_screen(handle, n, d, k):
+    # four assign groups, scores 32 at a time with a running top-3; blobs and structureless data
+    for X in (ko.make_blobs(n, d, k, seed=n)[0],
+              np.random.default_rng(k).uniform(-1.0, 1.0, size=(n, d)).astype(np.float32)):
+        C = X[np.random.default_rng(d).choice(n, size=k, replace=False)].copy()
+        labels, _ = handle.predict(dev(X), dev(C))
+        assert handle.screen_stats()[1] == 2
+        l_ref, best, second = ko.assign(X, C)
+        parity.assert_labels_match(labels.cpu().numpy(), best, second, l_ref)
+
+
 def test_fit_switches_to_the_split_kernel_when_the_screen_decides_too_little(handle, native):
     # one blob far from the origin shared by three centroids: a large share of its rows stays open in every pass
     rng = np.random.default_rng(17)
