@@ -14,6 +14,8 @@ NVCC_FLAGS = [
 ]
 if os.environ.get("B200KM_ENABLE_TRACE"):  # development builds: per-tile event clocks (tools/trace_view.py)
     NVCC_FLAGS.append("-DB200KM_ENABLE_TRACE")
+if os.environ.get("B200KM_UPD_BATCH"):  # development builds: update-warp batch size experiments
+    NVCC_FLAGS.append("-DB200KM_UPD_BATCH=" + os.environ["B200KM_UPD_BATCH"])
 
 
 def _stale(out, deps):

@@ -63,6 +63,10 @@ constexpr int kMaxND = 4;
 constexpr int kMaxD = 256;
 constexpr int kMaxK = 128;    // labels-only passes; larger k runs the split-TF32 kernel
 constexpr int kMaxKAcc = 32;  // passes with the update stage (register accumulators, lane = label in the sort)
+#ifndef B200KM_UPD_BATCH
+#define B200KM_UPD_BATCH 4
+#endif
+constexpr int kUpdBatch = B200KM_UPD_BATCH;  // rows of a label's run loaded together by an update warp
 constexpr int kHist = 40;  // label bins (k + 1) rounded up
 
 // Per-row verdict written by the screen kernel: bits 0-7 the computed best centroid (the row's provisional
@@ -808,15 +812,15 @@ __global__ void __launch_bounds__(kThreads, 1)
                 if (lab[li] >= 0) {
                     const int beg = s_base[sb][lab[li]], end = s_base[sb][lab[li] + 1];
 #pragma unroll 1
-                    for (int base = beg; base < end; base += 8) {
-                        unsigned int w[8];
-                        ulonglong2 v[8];
+                    for (int base = beg; base < end; base += kUpdBatch) {
+                        unsigned int w[kUpdBatch];
+                        ulonglong2 v[kUpdBatch];
 #pragma unroll
-                        for (int j = 0; j < 8; ++j) w[j] = perm[2 * (base + j)];  // past `end`: stale but valid offsets
+                        for (int j = 0; j < kUpdBatch; ++j) w[j] = perm[2 * (base + j)];  // past `end`: stale but valid offsets
 #pragma unroll
-                        for (int j = 0; j < 8; ++j) v[j] = *reinterpret_cast<const ulonglong2*>(colp + (w[j] ^ c16));
+                        for (int j = 0; j < kUpdBatch; ++j) v[j] = *reinterpret_cast<const ulonglong2*>(colp + (w[j] ^ c16));
 #pragma unroll
-                        for (int j = 0; j < 8; ++j) {
+                        for (int j = 0; j < kUpdBatch; ++j) {
                             add2_if(acc[li][0], v[j].x, base + j, end);
                             add2_if(acc[li][1], v[j].y, base + j, end);
                         }
