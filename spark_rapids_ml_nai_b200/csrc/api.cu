@@ -93,7 +93,9 @@ struct b200km_handle {
     int path = B200KM_PATH_AUTO;
     const char* last_path = "none";
     // workspace
-    IterState* d_state = nullptr;
+    IterState* d_state = nullptr;  // [1 + kRing]: the live state, then one snapshot per ring slot
+    cudaStream_t side = nullptr;   // carries the snapshots to the host beside the compute stream
+    cudaEvent_t evm[kRing] = {};   // "iteration finalized" on the compute stream
     IterState* h_state = nullptr;  // pinned ring [kRing] + 1 slot for the final read
     double* h_scalar = nullptr;    // pinned
     cudaEvent_t ev[kRing] = {};
@@ -137,6 +139,9 @@ int free_ws(b200km_handle* h) {
     if (h->h_scalar) cudaFreeHost(h->h_scalar);
     for (auto& e : h->ev)
         if (e) cudaEventDestroy(e);
+    for (auto& e : h->evm)
+        if (e) cudaEventDestroy(e);
+    if (h->side) cudaStreamDestroy(h->side);
     for (auto& e : h->pev)
         if (e) cudaEventDestroy(e);
     return 0;
@@ -230,7 +235,7 @@ int run_pass(b200km_handle* h, bool use_tc, const float* X, int64_t n, int d, in
         h->last_kernel = screen ? 2 : 1;
         if (rec) CU_TRY(cudaEventRecord(h->pev[2 * h->prof_n + 1], s));
         if (rec) h->prof_n++;
-        h->launches += screen ? 4 : 2;  // operand preparation (+ distance table, exact fix-up) + the fused kernel
+        h->launches += screen ? 3 : 2;  // operand preparation, the fused kernel (+ the exact fix-up)
         return 0;
     }
     if (!labels) labels = h->d_labels;
@@ -280,13 +285,21 @@ int b200km_create(int device, int rank, int nranks, const void* uid128, b200km_h
     h->device = device;
     h->rank = rank;
     h->nranks = nranks;
-    if (cudaMalloc((void**)&h->d_state, sizeof(IterState)) != cudaSuccess ||
-        cudaMemset(h->d_state, 0, sizeof(IterState)) != cudaSuccess ||
+    if (cudaMalloc((void**)&h->d_state, sizeof(IterState) * (1 + kRing)) != cudaSuccess ||
+        cudaMemset(h->d_state, 0, sizeof(IterState) * (1 + kRing)) != cudaSuccess ||
+        cudaStreamCreateWithFlags(&h->side, cudaStreamNonBlocking) != cudaSuccess ||
         cudaMallocHost((void**)&h->h_state, sizeof(IterState) * (kRing + 1)) != cudaSuccess ||
         cudaMallocHost((void**)&h->h_scalar, sizeof(double) * 8) != cudaSuccess) {
         free_ws(h);
         delete h;
         return fail("handle allocation failed: %s", cudaGetErrorString(cudaGetLastError()));
+    }
+    for (auto& e : h->evm) {
+        if (cudaEventCreateWithFlags(&e, cudaEventDisableTiming) != cudaSuccess) {
+            free_ws(h);
+            delete h;
+            return fail("cudaEventCreate failed");
+        }
     }
     for (auto& e : h->ev) {
         if (cudaEventCreateWithFlags(&e, cudaEventDisableTiming) != cudaSuccess) {
@@ -437,11 +450,17 @@ int b200km_fit(b200km_handle* h, const float* X, int64_t n_local, int d, int k, 
         if (run_pass(h, use_tc, X, n_local, d, k, h->d_C, nullptr, nullptr, h->d_acc, true, it == 0, s)) return 1;
         if (h->nranks > 1)
             NCCL_TRY(g_nccl.AllReduce(h->d_acc, h->d_acc, (size_t)acc_len, ncclFloat64, ncclSum, h->comm, s));
-        launch_finalize(h->d_C, k, d, h->d_cnorm, h->d_acc, h->d_shift, h->d_shift + h->k_cap, tol, h->d_state, s);
+        launch_finalize(h->d_C, k, d, h->d_cnorm, h->d_acc, h->d_shift, h->d_shift + h->k_cap, tol, h->d_state,
+                        h->d_state + 1 + slot, s);
         h->launches += 1;
         CU_TRY(cudaGetLastError());
-        CU_TRY(cudaMemcpyAsync(&h->h_state[slot], h->d_state, sizeof(IterState), cudaMemcpyDeviceToHost, s));
-        CU_TRY(cudaEventRecord(h->ev[slot], s));
+        // the host looks at the state kRing iterations later; the copy rides a side stream so that the next
+        // pass starts right behind finalize
+        CU_TRY(cudaEventRecord(h->evm[slot], s));
+        CU_TRY(cudaStreamWaitEvent(h->side, h->evm[slot], 0));
+        CU_TRY(cudaMemcpyAsync(&h->h_state[slot], h->d_state + 1 + slot, sizeof(IterState), cudaMemcpyDeviceToHost,
+                               h->side));
+        CU_TRY(cudaEventRecord(h->ev[slot], h->side));
     }
 
     double* d_inertia = h->d_acc + kd + k;

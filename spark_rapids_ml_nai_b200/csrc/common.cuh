@@ -39,7 +39,8 @@ void launch_refine(const float* X, int64_t n, int d, const float* C, int k, int3
 void launch_update(const float* X, int64_t n, int d, int k, const int32_t* labels, const float* best,
                    double* acc, IterState* st, bool honor_done, cudaStream_t s);
 void launch_sum_best(const float* best, int64_t n, double* out, cudaStream_t s);
+// snap: where the last block leaves a copy of *st once the iteration is complete (may be null)
 void launch_finalize(float* C, int k, int d, float* cnorm, double* acc, double* shift_part, double* cnt_part,
-                     double tol, IterState* st, cudaStream_t s);
+                     double tol, IterState* st, IterState* snap, cudaStream_t s);
 
 }  // namespace b200km

@@ -440,7 +440,7 @@ __global__ void __launch_bounds__(256) sum_best_kernel(const float* __restrict__
 __global__ void __launch_bounds__(128) finalize_kernel(float* __restrict__ C, int k, int d,
                                                        float* __restrict__ cnorm, double* __restrict__ acc,
                                                        double* __restrict__ shift_part, double* __restrict__ cnt_part,
-                                                       double tol, IterState* st) {
+                                                       double tol, IterState* st, IterState* snap) {
     __shared__ double red_s[4];
     __shared__ float red_c[4];
     if (st->done) return;
@@ -534,6 +534,9 @@ __global__ void __launch_bounds__(128) finalize_kernel(float* __restrict__ C, in
                 st->own[lane] = s_own[lane];
             }
         }
+        // a stable copy for the host: it is read asynchronously, while later iterations already change *st
+        __syncthreads();
+        if (threadIdx.x == 0 && snap) *snap = *st;
     }
 }
 
@@ -606,8 +609,8 @@ void launch_sum_best(const float* best, int64_t n, double* out, cudaStream_t s) 
 }
 
 void launch_finalize(float* C, int k, int d, float* cnorm, double* acc, double* shift_part, double* cnt_part,
-                     double tol, IterState* st, cudaStream_t s) {
-    finalize_kernel<<<k, 128, 0, s>>>(C, k, d, cnorm, acc, shift_part, cnt_part, tol, st);
+                     double tol, IterState* st, IterState* snap, cudaStream_t s) {
+    finalize_kernel<<<k, 128, 0, s>>>(C, k, d, cnorm, acc, shift_part, cnt_part, tol, st, snap);
 }
 
 }  // namespace b200km

@@ -164,10 +164,29 @@ __device__ __forceinline__ void trace_ev(const ScParams& p, int64_t it, int ev) 
 }
 
 // ------------------------------------------------------------------------------------------------
-// pd[a][b] = an upper bound of ||c_a - c_b|| (FP32 sum inflated by its own rounding bound)
-__global__ void __launch_bounds__(128) pairdist_kernel(const float* __restrict__ C, int k, int d,
-                                                       float* __restrict__ pd) {
-    const int pair = blockIdx.x * 4 + (threadIdx.x >> 5);
+// Operand preparation of a pass, one launch.  Blocks [0, split_blocks): the B operand out[2*k_pad][d_pad] (rows
+// [0,k_pad) = centroids rounded to TF32, rows [k_pad,2k_pad) = the TF32-rounded remainders, zero padded); the
+// other blocks: pd[a][b] = an upper bound of ||c_a - c_b|| (FP32 sum inflated by its own rounding bound), one
+// warp per pair.
+__global__ void __launch_bounds__(128) screen_prep_kernel(const float* __restrict__ C, int k, int d, int k_pad,
+                                                          int d_pad, int split_blocks, float* __restrict__ out,
+                                                          float* __restrict__ pd) {
+    if ((int)blockIdx.x < split_blocks) {
+        const int total = k_pad * d_pad;
+        for (int idx = blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += split_blocks * blockDim.x) {
+            const int j = idx / d_pad, i = idx - j * d_pad;
+            float hi = 0.f, lo = 0.f;
+            if (j < k && i < d) {
+                const float c = C[(size_t)j * d + i];
+                hi = __uint_as_float(tf32_round(__float_as_uint(c)));
+                lo = __uint_as_float(tf32_round(__float_as_uint(c - hi)));
+            }
+            out[idx] = hi;
+            out[(size_t)total + idx] = lo;
+        }
+        return;
+    }
+    const int pair = ((int)blockIdx.x - split_blocks) * 4 + (threadIdx.x >> 5);
     if (pair >= k * k) return;
     const int a = pair / k, b = pair - a * k;
     const int lane = threadIdx.x & 31;
@@ -988,8 +1007,12 @@ int screen_pass(TcWorkspace* ws, const float* X, int64_t n, int d, int k, const 
         }
         attr_set = true;
     }
-    launch_split_centroids(C, k, d, pl.k_pad, pl.d_pad, (float*)ws->d_buf, s);
-    pairdist_kernel<<<(k * k + 3) / 4, 128, 0, s>>>(C, k, d, (float*)ws->d_pd);
+    {
+        int split_blocks = (pl.k_pad * pl.d_pad + 127) / 128;
+        if (split_blocks > kNumSMs) split_blocks = kNumSMs;
+        screen_prep_kernel<<<split_blocks + (k * k + 3) / 4, 128, 0, s>>>(C, k, d, pl.k_pad, pl.d_pad, split_blocks,
+                                                                         (float*)ws->d_buf, (float*)ws->d_pd);
+    }
     ScParams p;
     p.n = n;
     p.num_tiles = (n + kTileM - 1) / kTileM;
