@@ -189,6 +189,16 @@ int ensure_ws(b200km_handle* h, int64_t n, int d, int k, bool need_row_bufs) {
     return 0;
 }
 
+// Adds the kernel launches issued inside its scope (counted at the launch sites) to the handle's counter.
+struct LaunchScope {
+    b200km_handle* h;
+    unsigned long long start;
+    explicit LaunchScope(b200km_handle* hh) : h(hh), start(g_launches) {}
+    ~LaunchScope() {
+        if (h) h->launches += g_launches - start;
+    }
+};
+
 int check_shape(const b200km_handle* h, const void* X, int64_t n, int d, int k) {
     if (!h) return fail("null handle");
     if (!X && n > 0) return fail("X is null");
@@ -235,7 +245,6 @@ int run_pass(b200km_handle* h, bool use_tc, const float* X, int64_t n, int d, in
         h->last_kernel = screen ? 2 : 1;
         if (rec) CU_TRY(cudaEventRecord(h->pev[2 * h->prof_n + 1], s));
         if (rec) h->prof_n++;
-        h->launches += screen ? 3 : 2;  // operand preparation, the fused kernel (+ the exact fix-up)
         return 0;
     }
     if (!labels) labels = h->d_labels;
@@ -246,7 +255,6 @@ int run_pass(b200km_handle* h, bool use_tc, const float* X, int64_t n, int d, in
     if (rec) h->prof_n++;
     launch_refine(X, n, d, C, k, labels, best, h->d_state, h->d_work, honor_done, s);
     if (acc) launch_update(X, n, d, k, labels, best, acc, h->d_state, honor_done, s);
-    h->launches += acc ? 3 : 2;
     CU_TRY(cudaGetLastError());
     return 0;
 }
@@ -423,6 +431,7 @@ int b200km_fit(b200km_handle* h, const float* X, int64_t n_local, int d, int k, 
     if (max_iter < 0) return fail("max_iter=%d < 0", max_iter);
     cudaStream_t s = (cudaStream_t)stream;
     CU_TRY(cudaSetDevice(h->device));
+    LaunchScope scope(h);
     bool use_tc = false;
     if (pick_path(h, X, d, k, true, &use_tc)) return 1;
     if (ensure_ws(h, n_local, d, k, true)) return 1;
@@ -433,7 +442,6 @@ int b200km_fit(b200km_handle* h, const float* X, int64_t n_local, int d, int k, 
     CU_TRY(cudaMemcpyAsync(h->d_C, init_centroids, sizeof(float) * kd, cudaMemcpyDeviceToDevice, s));
     if (!use_tc) launch_rownorm(X, n_local, d, h->d_xnorm, s);
     launch_prep(h->d_C, k, d, h->d_cnorm, h->d_acc, acc_len, h->d_state, true, s);
-    h->launches += use_tc ? 1 : 2;
     CU_TRY(cudaGetLastError());
 
     for (int it = 0; it < max_iter; ++it) {
@@ -452,7 +460,6 @@ int b200km_fit(b200km_handle* h, const float* X, int64_t n_local, int d, int k, 
             NCCL_TRY(g_nccl.AllReduce(h->d_acc, h->d_acc, (size_t)acc_len, ncclFloat64, ncclSum, h->comm, s));
         launch_finalize(h->d_C, k, d, h->d_cnorm, h->d_acc, h->d_shift, h->d_shift + h->k_cap, tol, h->d_state,
                         h->d_state + 1 + slot, s);
-        h->launches += 1;
         CU_TRY(cudaGetLastError());
         // the host looks at the state kRing iterations later; the copy rides a side stream so that the next
         // pass starts right behind finalize
@@ -469,7 +476,6 @@ int b200km_fit(b200km_handle* h, const float* X, int64_t n_local, int d, int k, 
         if (run_pass(h, use_tc, X, n_local, d, k, h->d_C, lab, h->d_best, nullptr, false, max_iter == 0, s)) return 1;
         CU_TRY(cudaMemsetAsync(d_inertia, 0, sizeof(double), s));
         launch_sum_best(h->d_best, n_local, d_inertia, s);
-        h->launches += 1;
         CU_TRY(cudaGetLastError());
         if (h->nranks > 1)
             NCCL_TRY(g_nccl.AllReduce(d_inertia, d_inertia, 1, ncclFloat64, ncclSum, h->comm, s));
@@ -490,6 +496,7 @@ int b200km_lloyd_step(b200km_handle* h, const float* X, int64_t n, int d, int k,
     if (!centroids || !sums_out || !counts_out || !inertia_out) return fail("null output / centroids");
     cudaStream_t s = (cudaStream_t)stream;
     CU_TRY(cudaSetDevice(h->device));
+    LaunchScope scope(h);
     bool use_tc = false;
     if (pick_path(h, X, d, k, true, &use_tc)) return 1;
     if (ensure_ws(h, n, d, k, true)) return 1;
@@ -502,7 +509,6 @@ int b200km_lloyd_step(b200km_handle* h, const float* X, int64_t n, int d, int k,
         if (run_pass(h, use_tc, X, n, d, k, centroids, labels_out, nullptr, h->d_acc, false, true, s)) return 1;
         if (h->last_kernel == 2) {
             screen_inertia_fix(centroids, k, d, h->d_acc, s);
-            h->launches += 1;
         }
     }
     CU_TRY(cudaMemcpyAsync(sums_out, h->d_acc, sizeof(double) * kd, cudaMemcpyDeviceToDevice, s));
@@ -519,6 +525,7 @@ int b200km_predict(b200km_handle* h, const float* X, int64_t n, int d, const flo
     if (!labels_out) return fail("labels_out is null");
     cudaStream_t s = (cudaStream_t)stream;
     CU_TRY(cudaSetDevice(h->device));
+    LaunchScope scope(h);
     bool use_tc = false;
     if (pick_path(h, X, d, k, false, &use_tc)) return 1;
     if (ensure_ws(h, n, d, k, true)) return 1;

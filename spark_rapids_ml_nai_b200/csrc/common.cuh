@@ -26,6 +26,24 @@ constexpr float kTieTol = 4e-6f;
 
 constexpr int kNumSMs = 148;
 
+// Per-device "already done" flags for one-time set-up that CUDA keeps per device (function attributes such
+// as the dynamic shared-memory opt-in): one process may drive several GPUs through several handles.
+constexpr int kMaxTrackedDevices = 64;
+struct PerDeviceOnce {
+    bool done[kMaxTrackedDevices] = {};
+    // index of the current device, or -1 when it cannot be tracked (the caller then repeats the set-up)
+    static int current() {
+        int dev = -1;
+        if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= kMaxTrackedDevices) return -1;
+        return dev;
+    }
+};
+
+// Kernel launches issued by this thread through the library's host launchers (every `<<<>>>` site counts
+// itself); the C-ABI layer reports the difference across a call as the handle's launch count.
+extern thread_local unsigned long long g_launches;
+inline void count_launch(int n = 1) { g_launches += (unsigned long long)n; }
+
 // ---- generic (SIMT) path, kernels_generic.cu ---------------------------------------------------
 void launch_prep(const float* C, int k, int d, float* cnorm, double* acc, int64_t acc_len,
                  IterState* st, bool reset_iter, cudaStream_t s);

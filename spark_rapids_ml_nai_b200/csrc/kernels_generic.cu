@@ -19,6 +19,8 @@
 
 namespace b200km {
 
+thread_local unsigned long long g_launches = 0;
+
 namespace {
 
 __device__ __forceinline__ float warp_sum(float v) {
@@ -547,6 +549,7 @@ void launch_prep(const float* C, int k, int d, float* cnorm, double* acc, int64_
                  bool reset_iter, cudaStream_t s) {
     if (acc) cudaMemsetAsync(acc, 0, sizeof(double) * (size_t)acc_len, s);
     cnorm_kernel<<<k, 128, 0, s>>>(C, k, d, cnorm, st, reset_iter ? 1 : 0);
+    count_launch();
 }
 
 void launch_rownorm(const float* X, int64_t n, int d, float* xnorm, cudaStream_t s) {
@@ -554,6 +557,7 @@ void launch_rownorm(const float* X, int64_t n, int d, float* xnorm, cudaStream_t
     int64_t blocks = (n + 7) / 8;
     if (blocks > kNumSMs * 16) blocks = kNumSMs * 16;
     rownorm_kernel<<<(unsigned)blocks, 256, 0, s>>>(X, n, d, xnorm);
+    count_launch();
 }
 
 void launch_assign_ffma(const float* X, int64_t n, int d, const float* C, int k, const float* cnorm,
@@ -569,6 +573,7 @@ void launch_assign_ffma(const float* X, int64_t n, int d, const float* C, int k,
     else
         assign_ffma_kernel<4><<<blocks, 256, 0, s>>>(X, n, d, C, k, cnorm, xnorm, labels, best, st, worklist,
                                                      honor_done ? 1 : 0, vec_ok);
+    count_launch();
 }
 
 void launch_refine(const float* X, int64_t n, int d, const float* C, int k, int32_t* labels, float* best,
@@ -577,6 +582,7 @@ void launch_refine(const float* X, int64_t n, int d, const float* C, int k, int3
     int64_t blocks = (n + 127) / 128;  // no more warps than could ever be needed
     if (blocks > kNumSMs * 2) blocks = kNumSMs * 2;
     refine_kernel<<<(unsigned)blocks, 256, 0, s>>>(X, d, C, k, labels, best, st, worklist, honor_done ? 1 : 0);
+    count_launch();
 }
 
 void launch_update(const float* X, int64_t n, int d, int k, const int32_t* labels, const float* best,
@@ -588,16 +594,19 @@ void launch_update(const float* X, int64_t n, int d, int k, const int32_t* label
     int64_t blocks = smem_acc ? kNumSMs : kNumSMs * 4;
     if (blocks > tiles) blocks = tiles;
     if (smem_acc) {
-        static bool attr_set = false;
-        if (!attr_set) {
+        static PerDeviceOnce attr_set;  // the opt-in is a per-device attribute
+        const int dev = PerDeviceOnce::current();
+        if (dev < 0 || !attr_set.done[dev]) {
             cudaFuncSetAttribute(update_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024);
-            attr_set = true;
+            if (dev >= 0) attr_set.done[dev] = true;
         }
         update_kernel<true><<<(unsigned)blocks, 256, smem, s>>>(X, n, d, k, labels, best, acc, st,
                                                                honor_done ? 1 : 0, tiles);
+        count_launch();
     } else {
         update_kernel<false><<<(unsigned)blocks, 256, 0, s>>>(X, n, d, k, labels, best, acc, st,
                                                               honor_done ? 1 : 0, tiles);
+        count_launch();
     }
 }
 
@@ -606,11 +615,13 @@ void launch_sum_best(const float* best, int64_t n, double* out, cudaStream_t s) 
     int64_t blocks = (n + 255) / 256;
     if (blocks > kNumSMs * 8) blocks = kNumSMs * 8;
     sum_best_kernel<<<(unsigned)blocks, 256, 0, s>>>(best, n, out);
+    count_launch();
 }
 
 void launch_finalize(float* C, int k, int d, float* cnorm, double* acc, double* shift_part, double* cnt_part,
                      double tol, IterState* st, IterState* snap, cudaStream_t s) {
     finalize_kernel<<<k, 128, 0, s>>>(C, k, d, cnorm, acc, shift_part, cnt_part, tol, st, snap);
+    count_launch();
 }
 
 }  // namespace b200km

@@ -946,6 +946,7 @@ const char* screen_last_error() { return g_sc_err; }
 
 void screen_inertia_fix(const float* C, int k, int d, double* acc, cudaStream_t s) {
     screen_inertia_fix_kernel<<<1, 256, 0, s>>>(C, k, d, acc);
+    count_launch();
 }
 
 int screen_pass(TcWorkspace* ws, const float* X, int64_t n, int d, int k, const float* C, const float* cnorm,
@@ -992,8 +993,9 @@ int screen_pass(TcWorkspace* ws, const float* X, int64_t n, int d, int k, const 
                   (uint32_t)pl.k_pad))
         return 1;
 
-    static bool attr_set = false;
-    if (!attr_set) {
+    static PerDeviceOnce attr_set;  // the opt-in is a per-device attribute
+    const int dev = PerDeviceOnce::current();
+    if (dev < 0 || !attr_set.done[dev]) {
         cudaFuncAttributes fa;
         if (cudaFuncGetAttributes(&fa, kmeans_screen_kernel) != cudaSuccess || (int)fa.sharedSizeBytes > kStaticSmem) {
             snprintf(g_sc_err, sizeof(g_sc_err), "unexpected static shared memory size of the screen kernel");
@@ -1005,13 +1007,14 @@ int screen_pass(TcWorkspace* ws, const float* X, int64_t n, int d, int k, const 
             snprintf(g_sc_err, sizeof(g_sc_err), "cannot raise dynamic shared memory to %d bytes", max_dyn);
             return 1;
         }
-        attr_set = true;
+        if (dev >= 0) attr_set.done[dev] = true;
     }
     {
         int split_blocks = (pl.k_pad * pl.d_pad + 127) / 128;
         if (split_blocks > kNumSMs) split_blocks = kNumSMs;
         screen_prep_kernel<<<split_blocks + (k * k + 3) / 4, 128, 0, s>>>(C, k, d, pl.k_pad, pl.d_pad, split_blocks,
                                                                          (float*)ws->d_buf, (float*)ws->d_pd);
+        count_launch();
     }
     ScParams p;
     p.n = n;
@@ -1051,14 +1054,17 @@ int screen_pass(TcWorkspace* ws, const float* X, int64_t n, int d, int k, const 
     p.off_pd = pl.off_pd;
     p.off_bar = pl.off_bar;
     p.trace = nullptr;
+#ifdef B200KM_ENABLE_TRACE  // development builds only (B200KM_ENABLE_TRACE=1 python -m ...build)
     const char* trace_path = getenv("B200KM_TRACE");
     if (trace_path && acc) {
-        cudaMalloc((void**)&p.trace, 256 * 16 * sizeof(unsigned long long));
-        cudaMemsetAsync(p.trace, 0, 256 * 16 * sizeof(unsigned long long), s);
+        cudaMalloc((void**)&p.trace, 4096 * sizeof(unsigned long long));
+        cudaMemsetAsync(p.trace, 0, 4096 * sizeof(unsigned long long), s);
     }
+#endif
     int64_t grid = p.num_tiles < kNumSMs ? p.num_tiles : kNumSMs;
     if (grid < 1) grid = 1;
     kmeans_screen_kernel<<<(unsigned)grid, kThreads, pl.total, s>>>(tmX, tmXt, tmC, tmCt, p);
+    count_launch();
     cudaError_t err = cudaGetLastError();
     if (err != cudaSuccess) {
         snprintf(g_sc_err, sizeof(g_sc_err), "screen kernel launch failed: %s", cudaGetErrorString(err));
@@ -1070,7 +1076,9 @@ int screen_pass(TcWorkspace* ws, const float* X, int64_t n, int d, int k, const 
         if (blocks < 1) blocks = 1;
         screen_fixup_kernel<<<(unsigned)blocks, 256, 0, s>>>(X, n, d, k, C, (const float*)ws->d_pd, info, labels, acc, st,
                                                              honor_done ? 1 : 0);
+        count_launch();
     }
+#ifdef B200KM_ENABLE_TRACE
     if (p.trace) {  // development aid: synchronous dump of CTA 0's per-tile event clocks
         static unsigned long long host[256 * 16];
         cudaStreamSynchronize(s);
@@ -1084,6 +1092,7 @@ int screen_pass(TcWorkspace* ws, const float* X, int64_t n, int d, int k, const 
             fclose(f);
         }
     }
+#endif
     return 0;
 }
 

@@ -799,6 +799,7 @@ void launch_split_centroids(const float* C, int k, int d, int k_pad, int d_pad, 
     int blocks = (total + 255) / 256;
     if (blocks > kNumSMs) blocks = kNumSMs;
     split_centroids_kernel<<<blocks, 256, 0, s>>>(C, k, d, k_pad, d_pad, out);
+    count_launch();
 }
 
 int tc_pass(TcWorkspace* ws, const float* X, int64_t n, int d, int k, const float* C, const float* cnorm,
@@ -831,8 +832,9 @@ int tc_pass(TcWorkspace* ws, const float* X, int64_t n, int d, int k, const floa
                   (uint32_t)pl.k_pad))
         return 1;
 
-    static bool attr_set = false;
-    if (!attr_set) {
+    static PerDeviceOnce attr_set;  // the opt-in is a per-device attribute
+    const int dev = PerDeviceOnce::current();
+    if (dev < 0 || !attr_set.done[dev]) {
         cudaFuncAttributes fa;
         if (cudaFuncGetAttributes(&fa, kmeans_fused_tc_kernel) != cudaSuccess ||
             (int)fa.sharedSizeBytes > kStaticSmem) {
@@ -845,7 +847,7 @@ int tc_pass(TcWorkspace* ws, const float* X, int64_t n, int d, int k, const floa
             snprintf(g_tc_err, sizeof(g_tc_err), "cannot raise dynamic shared memory to %d bytes", max_dyn);
             return 1;
         }
-        attr_set = true;
+        if (dev >= 0) attr_set.done[dev] = true;
     }
     launch_split_centroids(C, k, d, pl.k_pad, pl.d_pad, (float*)ws->d_buf, s);
     TcParams p;
@@ -879,19 +881,23 @@ int tc_pass(TcWorkspace* ws, const float* X, int64_t n, int d, int k, const floa
     p.off_xn = pl.off_xn;
     p.off_bar = pl.off_bar;
     p.trace = nullptr;
+#ifdef B200KM_ENABLE_TRACE  // development builds only
     const char* trace_path = getenv("B200KM_TRACE");
     if (trace_path && acc) {
         cudaMalloc((void**)&p.trace, 256 * 16 * sizeof(unsigned long long));
         cudaMemsetAsync(p.trace, 0, 256 * 16 * sizeof(unsigned long long), s);
     }
+#endif
     int64_t grid = p.num_tiles < kNumSMs ? p.num_tiles : kNumSMs;
     if (grid < 1) grid = 1;
     kmeans_fused_tc_kernel<<<(unsigned)grid, kThreads, pl.total, s>>>(tmX, tmXt, tmC, tmCt, p);
+    count_launch();
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) {
         snprintf(g_tc_err, sizeof(g_tc_err), "fused kernel launch failed: %s", cudaGetErrorString(e));
         return 1;
     }
+#ifdef B200KM_ENABLE_TRACE
     if (p.trace) {  // development aid: synchronous dump of CTA 0's per-tile event clocks
         static unsigned long long host[256 * 16];
         cudaStreamSynchronize(s);
@@ -905,6 +911,7 @@ int tc_pass(TcWorkspace* ws, const float* X, int64_t n, int d, int k, const floa
             fclose(f);
         }
     }
+#endif
     return 0;
 }
 
