@@ -40,6 +40,9 @@ typedef struct b200km_handle b200km_handle;
 #define B200KM_PATH_TC 2   /* tcgen05/TMEM/TMA fused pass (where the shape allows): the TF32 screen kernel with
                               float64 re-decision for passes that need no per-row distance, else split-TF32 */
 #define B200KM_PATH_TC_SPLIT 3 /* tcgen05 path, split-TF32 kernel for every pass */
+#define B200KM_PATH_GEMM 4     /* tcgen05 tile GEMM on a CTA pair (any k, d % 4 == 0): centroids streamed in N-tiles,
+                                  TF32 screen + exact fix-up, sums by a separate pass; AUTO takes it when k*d is
+                                  beyond the fused kernels' shared memory */
 
 /* init modes for b200km_init_centroids; reference: clustering.py:72 ("initMode" -> "init"),
  * values "random" and "k-means||" (clustering.py:185-186, tests/test_kmeans.py:84,93). */
@@ -74,7 +77,7 @@ int b200km_abort(b200km_handle* h);
  * not support makes the next compute call fail rather than fall back. */
 int b200km_set_path(b200km_handle* h, int path);
 
-/* Name of the path the last compute call on this handle used ("ffma" / "tc"). */
+/* Name of the path the last compute call on this handle used ("ffma" / "tc" / "gemm"). */
 const char* b200km_last_path(b200km_handle* h);
 
 /* 1 when the fused tcgen05 kernel can run this (d, k): with_update != 0 asks for the fit pass

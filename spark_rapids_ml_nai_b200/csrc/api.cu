@@ -112,8 +112,9 @@ struct b200km_handle {
     unsigned int* d_work = nullptr;
     size_t n_cap = 0;
     TcWorkspace tc;
+    GemmWorkspace gm;
     bool split_only = false;  // this fit saw too many float64 re-decisions in the screen kernel
-    int last_kernel = 0;      // 0 = FFMA kernels, 1 = split-TF32 fused kernel, 2 = screen kernel
+    int last_kernel = 0;      // 0 = FFMA kernels, 1 = split-TF32 fused kernel, 2 = screen kernel, 3 = tile GEMM
     // instrumentation (b200km_profile_*)
     bool prof = false;
     static constexpr int kProfMax = 256;
@@ -135,6 +136,7 @@ int free_ws(b200km_handle* h) {
     cudaFree(h->d_labels);
     cudaFree(h->d_work);
     tc_free(&h->tc);
+    gemm_free(&h->gm);
     if (h->h_state) cudaFreeHost(h->h_state);
     if (h->h_scalar) cudaFreeHost(h->h_scalar);
     for (auto& e : h->ev)
@@ -208,16 +210,24 @@ int check_shape(const b200km_handle* h, const void* X, int64_t n, int d, int k) 
     return 0;
 }
 
-// Picks the kernel path for this shape, honouring a forced path (and failing if it cannot run).
-int pick_path(b200km_handle* h, const float* X, int d, int k, bool with_acc, bool* use_tc) {
-    const bool can = tc_supported(X, d, k, with_acc);
-    if ((h->path == B200KM_PATH_TC || h->path == B200KM_PATH_TC_SPLIT) && !can)
+// Kernel family of a pass.
+enum Kind { KIND_FFMA = 0, KIND_TC = 1, KIND_GEMM = 2 };
+
+// Picks the kernel family for this shape, honouring a forced path (and failing if it cannot run).
+int pick_path(b200km_handle* h, const float* X, int d, int k, bool with_acc, int* kind) {
+    const bool can_tc = tc_supported(X, d, k, with_acc);
+    const bool can_gemm = gemm_supported(X, d, k);
+    if ((h->path == B200KM_PATH_TC || h->path == B200KM_PATH_TC_SPLIT) && !can_tc)
         return fail("tcgen05 path forced but not available for d=%d k=%d (needs d%%4==0, 16B-aligned X, "
                     "d<=%d, k<=%d and the split centroids%s to fit shared memory)", d, k, tc_max_d(), tc_max_k(),
                     with_acc ? " + float64 accumulators" : "");
-    const bool forced = h->path == B200KM_PATH_TC || h->path == B200KM_PATH_TC_SPLIT;
-    *use_tc = forced || (h->path == B200KM_PATH_AUTO && can);
-    h->last_path = *use_tc ? "tc" : "ffma";
+    if (h->path == B200KM_PATH_GEMM && !can_gemm)
+        return fail("tcgen05 tile-GEMM path forced but not available for d=%d k=%d (needs d%%4==0 and 16B-aligned X)", d, k);
+    if (h->path == B200KM_PATH_TC || h->path == B200KM_PATH_TC_SPLIT) *kind = KIND_TC;
+    else if (h->path == B200KM_PATH_GEMM) *kind = KIND_GEMM;
+    else if (h->path == B200KM_PATH_FFMA) *kind = KIND_FFMA;
+    else *kind = can_tc ? KIND_TC : (can_gemm ? KIND_GEMM : KIND_FFMA);
+    h->last_path = *kind == KIND_TC ? "tc" : (*kind == KIND_GEMM ? "gemm" : "ffma");
     return 0;
 }
 
@@ -225,8 +235,11 @@ int pick_path(b200km_handle* h, const float* X, int d, int k, bool with_acc, boo
 // labels / best: caller buffers, or nullptr when the caller does not need them (the FFMA kernels then use
 // the workspace arrays).  acc == nullptr -> assignment only.  On the tcgen05 path a pass that needs no
 // per-row distances runs the screen kernel, every other one the split-TF32 kernel.
-int run_pass(b200km_handle* h, bool use_tc, const float* X, int64_t n, int d, int k, const float* C,
-             int32_t* labels, float* best, double* acc, bool honor_done, bool xn_compute, cudaStream_t s) {
+// want_inertia: with acc, the inertia slot of acc has to be right (the tile-GEMM path then computes per-row distances).
+int run_pass(b200km_handle* h, int kind, const float* X, int64_t n, int d, int k, const float* C,
+             int32_t* labels, float* best, double* acc, bool honor_done, bool xn_compute, cudaStream_t s,
+             bool want_inertia = false) {
+    const bool use_tc = kind == KIND_TC;
     // the dominant kernel of the pass is bracketed by an event pair when profiling is on
     const bool rec = h->prof && h->prof_n < b200km_handle::kProfMax;
     if (rec) CU_TRY(cudaEventRecord(h->pev[2 * h->prof_n], s));
@@ -245,6 +258,23 @@ int run_pass(b200km_handle* h, bool use_tc, const float* X, int64_t n, int d, in
         h->last_kernel = screen ? 2 : 1;
         if (rec) CU_TRY(cudaEventRecord(h->pev[2 * h->prof_n + 1], s));
         if (rec) h->prof_n++;
+        return 0;
+    }
+    if (kind == KIND_GEMM) {
+        // tile GEMM on the tensor cores -> exact labels; distances and sums are separate (cheap) passes here
+        int32_t* lab = labels ? labels : h->d_labels;
+        float* xlo = reinterpret_cast<float*>(h->d_work);
+        if (xn_compute) launch_rownorm2(X, n, d, h->d_xnorm, xlo, s);
+        if (gemm_pass(&h->gm, X, n, d, k, C, h->d_cnorm, h->d_xnorm, xlo, lab, h->d_state, honor_done, s))
+            return fail("tcgen05 tile-GEMM pass failed: %s", gemm_last_error());
+        h->last_kernel = 3;
+        if (rec) CU_TRY(cudaEventRecord(h->pev[2 * h->prof_n + 1], s));
+        if (rec) h->prof_n++;
+        float* bst = best ? best : h->d_best;
+        if (best || (acc && want_inertia)) launch_rowdist(X, n, d, C, lab, bst, s);
+        else if (acc) CU_TRY(cudaMemsetAsync(bst, 0, sizeof(float) * (size_t)n, s));
+        if (acc) launch_update(X, n, d, k, lab, bst, acc, h->d_state, honor_done, s);
+        CU_TRY(cudaGetLastError());
         return 0;
     }
     if (!labels) labels = h->d_labels;
@@ -360,7 +390,7 @@ int b200km_abort(b200km_handle* h) {
 
 int b200km_set_path(b200km_handle* h, int path) {
     if (!h) return fail("null handle");
-    if (path < B200KM_PATH_AUTO || path > B200KM_PATH_TC_SPLIT) return fail("unknown path %d", path);
+    if (path < B200KM_PATH_AUTO || path > B200KM_PATH_GEMM) return fail("unknown path %d", path);
     h->path = path;
     return 0;
 }
@@ -418,6 +448,7 @@ int b200km_query_workspace(int64_t n, int d, int k, size_t* bytes_out) {
     size_t b = sizeof(double) * (kd + k + 1 + 64) + sizeof(double) * (k + 64) + sizeof(float) * (k + 64) +
                sizeof(float) * (kd + kd / 8 + 64) + 16 * ((size_t)n + (size_t)n / 8 + 256) + sizeof(IterState);
     b += tc_workspace_bytes(d, k) > screen_workspace_bytes(d, k) ? tc_workspace_bytes(d, k) : screen_workspace_bytes(d, k);
+    if (!tc_supported(nullptr, d, k, true)) b += gemm_workspace_bytes(n, d, k);
     *bytes_out = b;
     return 0;
 }
@@ -432,15 +463,15 @@ int b200km_fit(b200km_handle* h, const float* X, int64_t n_local, int d, int k, 
     cudaStream_t s = (cudaStream_t)stream;
     CU_TRY(cudaSetDevice(h->device));
     LaunchScope scope(h);
-    bool use_tc = false;
-    if (pick_path(h, X, d, k, true, &use_tc)) return 1;
+    int kind = KIND_FFMA;
+    if (pick_path(h, X, d, k, true, &kind)) return 1;
     if (ensure_ws(h, n_local, d, k, true)) return 1;
     const size_t kd = (size_t)k * d;
     const int64_t acc_len = (int64_t)kd + k + 1;
 
     h->split_only = false;
     CU_TRY(cudaMemcpyAsync(h->d_C, init_centroids, sizeof(float) * kd, cudaMemcpyDeviceToDevice, s));
-    if (!use_tc) launch_rownorm(X, n_local, d, h->d_xnorm, s);
+    if (kind == KIND_FFMA) launch_rownorm(X, n_local, d, h->d_xnorm, s);
     launch_prep(h->d_C, k, d, h->d_cnorm, h->d_acc, acc_len, h->d_state, true, s);
     CU_TRY(cudaGetLastError());
 
@@ -455,7 +486,7 @@ int b200km_fit(b200km_handle* h, const float* X, int64_t n_local, int d, int k, 
             const double seen = (double)n_local * (double)(it - kRing + 1);
             if (!h->split_only && (double)h->h_state[slot].screen_refined > 0.02 * seen) h->split_only = true;
         }
-        if (run_pass(h, use_tc, X, n_local, d, k, h->d_C, nullptr, nullptr, h->d_acc, true, it == 0, s)) return 1;
+        if (run_pass(h, kind, X, n_local, d, k, h->d_C, nullptr, nullptr, h->d_acc, true, it == 0, s)) return 1;
         if (h->nranks > 1)
             NCCL_TRY(g_nccl.AllReduce(h->d_acc, h->d_acc, (size_t)acc_len, ncclFloat64, ncclSum, h->comm, s));
         launch_finalize(h->d_C, k, d, h->d_cnorm, h->d_acc, h->d_shift, h->d_shift + h->k_cap, tol, h->d_state,
@@ -473,7 +504,7 @@ int b200km_fit(b200km_handle* h, const float* X, int64_t n_local, int d, int k, 
     double* d_inertia = h->d_acc + kd + k;
     if (inertia_out || labels_out) {
         int32_t* lab = labels_out ? labels_out : h->d_labels;
-        if (run_pass(h, use_tc, X, n_local, d, k, h->d_C, lab, h->d_best, nullptr, false, max_iter == 0, s)) return 1;
+        if (run_pass(h, kind, X, n_local, d, k, h->d_C, lab, h->d_best, nullptr, false, max_iter == 0, s)) return 1;
         CU_TRY(cudaMemsetAsync(d_inertia, 0, sizeof(double), s));
         launch_sum_best(h->d_best, n_local, d_inertia, s);
         CU_TRY(cudaGetLastError());
@@ -497,16 +528,16 @@ int b200km_lloyd_step(b200km_handle* h, const float* X, int64_t n, int d, int k,
     cudaStream_t s = (cudaStream_t)stream;
     CU_TRY(cudaSetDevice(h->device));
     LaunchScope scope(h);
-    bool use_tc = false;
-    if (pick_path(h, X, d, k, true, &use_tc)) return 1;
+    int kind = KIND_FFMA;
+    if (pick_path(h, X, d, k, true, &kind)) return 1;
     if (ensure_ws(h, n, d, k, true)) return 1;
     const size_t kd = (size_t)k * d;
-    if (!use_tc) launch_rownorm(X, n, d, h->d_xnorm, s);
+    if (kind == KIND_FFMA) launch_rownorm(X, n, d, h->d_xnorm, s);
     launch_prep(centroids, k, d, h->d_cnorm, h->d_acc, (int64_t)kd + k + 1, h->d_state, true, s);
     CU_TRY(cudaGetLastError());
     h->split_only = false;
     if (n > 0) {
-        if (run_pass(h, use_tc, X, n, d, k, centroids, labels_out, nullptr, h->d_acc, false, true, s)) return 1;
+        if (run_pass(h, kind, X, n, d, k, centroids, labels_out, nullptr, h->d_acc, false, true, s, true)) return 1;
         if (h->last_kernel == 2) {
             screen_inertia_fix(centroids, k, d, h->d_acc, s);
         }
@@ -526,14 +557,14 @@ int b200km_predict(b200km_handle* h, const float* X, int64_t n, int d, const flo
     cudaStream_t s = (cudaStream_t)stream;
     CU_TRY(cudaSetDevice(h->device));
     LaunchScope scope(h);
-    bool use_tc = false;
-    if (pick_path(h, X, d, k, false, &use_tc)) return 1;
+    int kind = KIND_FFMA;
+    if (pick_path(h, X, d, k, false, &kind)) return 1;
     if (ensure_ws(h, n, d, k, true)) return 1;
-    if (!use_tc) launch_rownorm(X, n, d, h->d_xnorm, s);
+    if (kind == KIND_FFMA) launch_rownorm(X, n, d, h->d_xnorm, s);
     launch_prep(centroids, k, d, h->d_cnorm, nullptr, 0, h->d_state, false, s);
     CU_TRY(cudaGetLastError());
     h->split_only = false;
-    return run_pass(h, use_tc, X, n, d, k, centroids, labels_out, min_dist_out, nullptr, false, true, s);
+    return run_pass(h, kind, X, n, d, k, centroids, labels_out, min_dist_out, nullptr, false, true, s);
 }
 
 int b200km_init_centroids(b200km_handle* h, const float* X, int64_t n_local, int d, int k, int mode,

@@ -1,0 +1,803 @@
+// tcgen05 tile-GEMM path for k*d beyond shared memory: nearest centroid for any k and any d % 4 == 0.
+//
+// Two CTAs of a cluster (one SM pair) own 256 rows of X and walk all centroids in N-tiles of up to 256.  The
+// scores  x^.c_j - 0.5 ||c_j||^2  are one `tcgen05.mma.cta_group::2.kind::tf32` GEMM  [256 x d] . [d x N]  with
+//   A = the raw FP32 rows of X exactly as TMA wrote them (K-major, SWIZZLE_128B; the tensor core reads the top
+//       19 bits of each word, i.e. x truncated to TF32 = x^); each CTA holds its 128 rows,
+//   B = the TF32 split [c_hi ; c_lo] of the centroids (prepared per pass), streamed through a TMA ring in
+//       sub-chunks of 16 floats (SWIZZLE_64B), each CTA loading its half of the N rows,
+//   the norm folded in as one more K-step: A = a constant tile holding -0.5, B = the three-term TF32 split
+//       of ||c_j||^2, so the accumulator is the score itself and the epilogue only compares,
+//   D = FP32 accumulators in TMEM, two buffers of 256 columns: the epilogue of N-tile i overlaps the MMAs of i+1.
+// A stays resident in shared memory across the N-tiles when d <= 256; otherwise it streams with B.
+//
+// Epilogue (8 warps per CTA, two per TMEM lane quarter, each half of the columns): tcgen05.ld 32 scores at a
+// time, the centroid's index inside the 32 goes into the 5 low mantissa bits, a tournament yields the three
+// largest, merged into the row's running triple.  After the last N-tile the row's best / second / third give
+//   D_j = ||x||^2 - 2 score_j,
+// and the same rigorous screen as kernels_screen.cu decides whether the TF32 view of x decided the row: the
+// error of a margin D_a - D_b is 2 (x - x^).(c_a - c_b) + FP32 rounding <= 2 ||x - x^|| (r_a + r_b) + eps with
+// r_j = ||x - c_j|| (triangle inequality: no k x k table needed).  Rows that fail are appended to a list and
+// decided exactly (FP32 differences, float64 when those tie) by gemm_fixup_kernel; labels are exact for every
+// row.  Sums are accumulated by a separate pass (this regime is tensor-bound: a second read of X is cheap).
+//
+// TMA loads here are plain (no multicast) and read only this GPU's memory.
+//
+// Replaces cuML's fusedL2NN behind reference python/src/spark_rapids_ml/clustering.py:367-370 (fit) and
+// :493-497 (predict) for the shapes of BASELINE.json C3 / C5 and the reference's own k=1000 x d=3000 benchmark
+// (python/benchmark/databricks/run_benchmark.sh:46-55).
+#include "tc.cuh"
+#include "tc_ptx.cuh"
+
+#include <cfloat>
+#include <climits>
+#include <cstdio>
+
+namespace b200km {
+
+namespace {
+
+using namespace tcx;
+
+thread_local char g_gm_err[512] = "";
+
+constexpr int kGmThreads = 384;  // warp 0 TMA, 1 MMA issue / relay, 2 TMEM, 3 spare, 4-11 epilogue
+constexpr int kEpiWarp0 = 4;
+constexpr int kRowsCta = 128;
+constexpr int kRowsPair = 256;
+constexpr int kASlotBytes = kRowsCta * 128;  // 128 rows x 32 floats, SWIZZLE_128B
+constexpr int kMaxNA = 8, kMaxNB = 8;
+constexpr int kConstABytes = kRowsCta * 32;  // the -0.5 tile: 128 rows x 8 floats, SWIZZLE_32B
+constexpr int kScrBytes = 5 * kRowsCta * 4;  // hand-over of the column halves: (b1, cb1, b2, cb2, b3) per row
+constexpr int kBarBytes = 512;
+constexpr int kMaxSmem = 227 * 1024;
+constexpr float kCnPad = 1e30f;  // "norm" of the padded centroid columns: their score is -5e29
+
+struct GmParams {
+    int64_t n;
+    int64_t num_tiles;  // 256-row tiles
+    int d, k, k_pad;
+    int n_sub;     // K sub-chunks of 16 floats
+    int ntile;     // N of one MMA (multiple of 64, <= 256)
+    int n_ntiles;  // k_pad / ntile
+    int NA, NB, resident;
+    int b_slot_bytes;
+    const float* xnorm;
+    const float* xlo;
+    int32_t* labels;
+    uint2* open;  // (row, runner-up | mode << 24) of every row the TF32 scores did not decide
+    unsigned int* open_count;
+    IterState* st;
+    int honor_done;
+    float tol_x, eps_rel, abs_rel;
+    int off_a, off_b, off_ac, off_scr, off_bar;
+};
+
+// ---- cluster / cta_group::2 PTX ------------------------------------------------------------------
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+    uint32_t r;
+    asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+    return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+    asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+// address of the same shared-memory offset in CTA `rank` of the cluster
+__device__ __forceinline__ uint32_t map_to_cta(uint32_t addr, uint32_t rank) {
+    uint32_t r;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(addr), "r"(rank));
+    return r;
+}
+__device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_addr) {
+    asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
+}
+// arrives on the barrier at this offset in both CTAs of the pair once all MMAs issued so far have completed
+__device__ __forceinline__ void tc_commit_pair(uint32_t bar) {
+    asm volatile(
+        "tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(bar),
+        "h"((unsigned short)3)
+        : "memory");
+}
+// D[tmem, both CTAs] (+)= A[smem desc] * B[smem desc], kind::tf32, M = 256 across the CTA pair
+__device__ __forceinline__ void mma_tf32_ss2(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc,
+                                             uint32_t accumulate) {
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::2.kind::tf32 [%0], %1, %2, %3, p;\n\t"
+        "}" ::"r"(d_tmem),
+        "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&r)[32]) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x32.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+        "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+          "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]),
+          "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]),
+          "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+        : "r"(taddr)
+        : "memory");
+}
+
+// The three largest of 32 keys by a tournament of sorted lists (pairs -> triples -> ...); the third largest of
+// two descending triples is max(a3, b3, min(a1,b2), min(a2,b1)).
+__device__ __forceinline__ void top3max_of_32(const float (&key)[32], float& o1, float& o2, float& o3) {
+    float m1[16], m2[16], m3[8];
+#pragma unroll
+    for (int i = 0; i < 16; ++i) {
+        m1[i] = fmaxf(key[2 * i], key[2 * i + 1]);
+        m2[i] = fminf(key[2 * i], key[2 * i + 1]);
+    }
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        const float a1 = m1[2 * i], a2 = m2[2 * i], b1 = m1[2 * i + 1], b2 = m2[2 * i + 1];
+        m1[i] = fmaxf(a1, b1);
+        m2[i] = fmaxf(fminf(a1, b1), fmaxf(a2, b2));
+        m3[i] = fmaxf(fminf(a1, b2), fminf(a2, b1));
+    }
+#pragma unroll
+    for (int nn = 8; nn > 1; nn >>= 1) {
+#pragma unroll
+        for (int i = 0; i < nn / 2; ++i) {
+            const float a1 = m1[2 * i], a2 = m2[2 * i], a3 = m3[2 * i];
+            const float b1 = m1[2 * i + 1], b2 = m2[2 * i + 1], b3 = m3[2 * i + 1];
+            m1[i] = fmaxf(a1, b1);
+            m2[i] = fmaxf(fminf(a1, b1), fmaxf(a2, b2));
+            m3[i] = fmaxf(fmaxf(a3, b3), fmaxf(fminf(a1, b2), fminf(a2, b1)));
+        }
+    }
+    o1 = m1[0];
+    o2 = m2[0];
+    o3 = m3[0];
+}
+
+// Merges the descending triple (o1, o2, o3) (origins oc1, oc2) into the running one.
+__device__ __forceinline__ void merge3(float& b1, int& cb1, float& b2, int& cb2, float& b3, float o1, int oc1, float o2,
+                                       int oc2, float o3) {
+    const bool w1 = o1 > b1;
+    const float n1 = w1 ? o1 : b1;
+    const int n1c = w1 ? oc1 : cb1;
+    const float l1 = w1 ? b1 : o1;  // the loser of the heads
+    const int l1c = w1 ? cb1 : oc1;
+    const bool w2 = o2 > b2;
+    const float m2 = w2 ? o2 : b2;
+    const int m2c = w2 ? oc2 : cb2;
+    const bool w3 = m2 > l1;
+    const float n3 = fmaxf(fmaxf(b3, o3), fmaxf(fminf(b1, o2), fminf(b2, o1)));
+    b1 = n1;
+    cb1 = n1c;
+    b2 = w3 ? m2 : l1;
+    cb2 = w3 ? m2c : l1c;
+    b3 = n3;
+}
+
+// ------------------------------------------------------------------------------------------------
+// Operand preparation of a pass.  bsplit[2*k_pad][d_pad]: rows [0,k_pad) = centroids rounded to TF32, rows
+// [k_pad, 2k_pad) = the TF32-rounded remainders, zero padded.  cn3[k_pad][8]: columns 0-2 = three-term TF32 split
+// of ||c_j||^2 (kCnPad for padded rows), columns 3-7 zero.
+__global__ void __launch_bounds__(256) gemm_prep_kernel(const float* __restrict__ C, const float* __restrict__ cnorm,
+                                                        int k, int d, int k_pad, int d_pad, float* __restrict__ bsplit,
+                                                        float* __restrict__ cn3) {
+    const size_t total = (size_t)k_pad * d_pad;
+    const size_t stride = (size_t)gridDim.x * blockDim.x;
+    for (size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += stride) {
+        const int j = (int)(idx / d_pad), i = (int)(idx - (size_t)j * d_pad);
+        float hi = 0.f, lo = 0.f;
+        if (j < k && i < d) {
+            const float c = C[(size_t)j * d + i];
+            hi = __uint_as_float(tf32_round(__float_as_uint(c)));
+            lo = __uint_as_float(tf32_round(__float_as_uint(c - hi)));
+        }
+        bsplit[idx] = hi;
+        bsplit[total + idx] = lo;
+    }
+    for (size_t j = (size_t)blockIdx.x * blockDim.x + threadIdx.x; j < (size_t)k_pad; j += stride) {
+        const float v = j < (size_t)k ? cnorm[j] : kCnPad;
+        const float a = __uint_as_float(tf32_round(__float_as_uint(v)));
+        const float b = __uint_as_float(tf32_round(__float_as_uint(v - a)));
+        const float c = __uint_as_float(tf32_round(__float_as_uint((v - a) - b)));
+        float4* o = reinterpret_cast<float4*>(cn3 + j * 8);
+        o[0] = make_float4(a, b, c, 0.f);
+        o[1] = make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+}
+
+// ||x||^2 and ||x - trunc_tf32(x)||^2 per row: one warp per row (once per fit / predict call).
+__global__ void __launch_bounds__(256) rownorm2_kernel(const float* __restrict__ X, int64_t n, int d,
+                                                       float* __restrict__ xnorm, float* __restrict__ xlo) {
+    const int lane = threadIdx.x & 31;
+    const int64_t warp = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    const int64_t nwarps = (int64_t)gridDim.x * (blockDim.x >> 5);
+    const int nch = d >> 2;
+    for (int64_t r = warp; r < n; r += nwarps) {
+        const float4* row = reinterpret_cast<const float4*>(X + r * d);
+        float s = 0.f, l = 0.f;
+        for (int c = lane; c < nch; c += 32) {
+            const float4 v = __ldg(row + c);
+            const float e[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+            for (int t = 0; t < 4; ++t) {
+                s = fmaf(e[t], e[t], s);
+                const float rr = e[t] - __uint_as_float(tf32_trunc(__float_as_uint(e[t])));  // exact
+                l = fmaf(rr, rr, l);
+            }
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            s += __shfl_xor_sync(0xffffffffu, s, o);
+            l += __shfl_xor_sync(0xffffffffu, l, o);
+        }
+        if (lane == 0) {
+            xnorm[r] = s;
+            xlo[r] = l;
+        }
+    }
+}
+
+// ---- exact decisions -------------------------------------------------------------------------------
+__device__ __forceinline__ float sqdist_f32(const float4* __restrict__ x4, const float4* __restrict__ c4, int nchunks,
+                                            int lane) {
+    float s = 0.f;
+    for (int ch = lane; ch < nchunks; ch += 32) {
+        const float4 xv = __ldg(x4 + ch), cv = __ldg(c4 + ch);
+        const float d0 = xv.x - cv.x, d1 = xv.y - cv.y, d2 = xv.z - cv.z, d3 = xv.w - cv.w;
+        s += fmaf(d0, d0, d1 * d1) + fmaf(d2, d2, d3 * d3);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+    return s;
+}
+__device__ __forceinline__ double sqdist_f64(const float* __restrict__ x, const float* __restrict__ c, int d, int lane) {
+    double s = 0.0;
+    for (int i = lane; i < d; i += 32) {
+        const double df = (double)__ldg(x + i) - (double)__ldg(c + i);
+        s = fma(df, df, s);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+    return s;
+}
+
+// One warp per listed row.  mode 0: exactly the computed best (labels[row]) against the runner-up; mode 1: every
+// centroid.  FP32 squared differences (no cancellation), float64 among those that tie; ties keep the lowest index.
+__global__ void __launch_bounds__(256) gemm_fixup_kernel(const float* __restrict__ X, int d, int k,
+                                                         const float* __restrict__ C, const uint2* __restrict__ open,
+                                                         const unsigned int* __restrict__ open_count,
+                                                         int32_t* __restrict__ labels, IterState* st, int honor_done) {
+    if (honor_done && st->done) return;
+    const unsigned int count = *open_count;
+    const int lane = threadIdx.x & 31;
+    const unsigned int warp0 = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    const unsigned int nwarps = gridDim.x * (blockDim.x >> 5);
+    const int nchunks = d >> 2;
+    for (unsigned int w = warp0; w < count; w += nwarps) {
+        const uint2 e = open[w];
+        const int64_t row = e.x;
+        const int i2 = (int)(e.y & 0xFFFFFFu);
+        const int mode = (int)(e.y >> 24);
+        const int i1 = labels[row];
+        const float* x = X + (size_t)row * d;
+        const float4* x4 = reinterpret_cast<const float4*>(x);
+        int bi;
+        if (mode == 0) {
+            const int ja = min(i1, i2), jb = max(i1, i2);
+            const float sa = sqdist_f32(x4, reinterpret_cast<const float4*>(C + (size_t)ja * d), nchunks, lane);
+            const float sb = sqdist_f32(x4, reinterpret_cast<const float4*>(C + (size_t)jb * d), nchunks, lane);
+            bi = sb < sa ? jb : ja;
+            if (fabsf(sa - sb) <= 4e-6f * (sa + sb)) {
+                const double da = sqdist_f64(x, C + (size_t)ja * d, d, lane);
+                const double db = sqdist_f64(x, C + (size_t)jb * d, d, lane);
+                bi = db < da ? jb : ja;
+            }
+        } else {
+            float f1 = FLT_MAX, f2 = FLT_MAX;
+            bi = 0;
+            for (int j = 0; j < k; ++j) {
+                const float sum = sqdist_f32(x4, reinterpret_cast<const float4*>(C + (size_t)j * d), nchunks, lane);
+                if (sum < f1) {  // ascending index order: ties keep the lowest
+                    f2 = f1;
+                    f1 = sum;
+                    bi = j;
+                } else {
+                    f2 = fminf(f2, sum);
+                }
+            }
+            if (f2 < FLT_MAX && (f2 - f1) <= 4e-6f * (f1 + f2)) {
+                // float64 among the centroids inside the FP32 band of the best
+                const float lim = f1 + 8e-6f * (f1 + f2);
+                double bd = DBL_MAX;
+                for (int j = 0; j < k; ++j) {
+                    const float sum = sqdist_f32(x4, reinterpret_cast<const float4*>(C + (size_t)j * d), nchunks, lane);
+                    if (sum > lim) continue;
+                    const double s64 = sqdist_f64(x, C + (size_t)j * d, d, lane);
+                    if (s64 < bd) {
+                        bd = s64;
+                        bi = j;
+                    }
+                }
+            }
+        }
+        if (bi != i1 && lane == 0) labels[row] = bi;
+    }
+    if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(&st->screen_refined, count);
+}
+
+// best[i] = ||x_i - c_label(i)||^2 from FP32 differences: one warp per row.
+__global__ void __launch_bounds__(256) rowdist_kernel(const float* __restrict__ X, int64_t n, int d,
+                                                      const float* __restrict__ C, const int32_t* __restrict__ labels,
+                                                      float* __restrict__ best) {
+    const int lane = threadIdx.x & 31;
+    const int64_t warp = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    const int64_t nwarps = (int64_t)gridDim.x * (blockDim.x >> 5);
+    const int nch = d >> 2;
+    for (int64_t r = warp; r < n; r += nwarps) {
+        const float v = sqdist_f32(reinterpret_cast<const float4*>(X + r * d),
+                                   reinterpret_cast<const float4*>(C + (size_t)labels[r] * d), nch, lane);
+        if (lane == 0) best[r] = v;
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kGmThreads, 1)
+    kmeans_gemm_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ CUtensorMap tmB,
+                       const __grid_constant__ CUtensorMap tmCn, const GmParams p) {
+    if (p.honor_done && p.st->done) return;  // both CTAs of a pair read the same flag
+
+    extern __shared__ __align__(1024) uint8_t smem_raw[];
+    uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
+    const uint32_t smem_base = smem_u32(smem);
+
+    const int warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
+    const uint32_t rank = cluster_ctarank();
+    const int64_t cluster_id = blockIdx.x >> 1;
+    const int64_t n_clusters = gridDim.x >> 1;
+    const int NA = p.NA, NB = p.NB;
+    const int N = p.ntile;
+    const int halfN = N >> 1;
+
+    // barrier table (8 bytes each)
+    const uint32_t bar0 = smem_base + p.off_bar;
+    const uint32_t a_full0 = bar0, a_empty0 = bar0 + 64, b_full0 = bar0 + 128, b_empty0 = bar0 + 192,
+                   d_full0 = bar0 + 256, d_empty0 = bar0 + 272;
+    uint32_t* tmem_slot = (uint32_t*)(smem + p.off_bar + 288);
+
+    if (threadIdx.x == 0) {
+        // the leader's full barriers also collect the peer's "my half has landed" arrival
+        const uint32_t full_count = rank == 0 ? 2u : 1u;
+        for (int s = 0; s < kMaxNA; ++s) {
+            mbar_init(a_full0 + 8u * s, full_count);
+            mbar_init(a_empty0 + 8u * s, 1);
+        }
+        for (int s = 0; s < kMaxNB; ++s) {
+            mbar_init(b_full0 + 8u * s, full_count);
+            mbar_init(b_empty0 + 8u * s, 1);
+        }
+        for (int s = 0; s < 2; ++s) {
+            mbar_init(d_full0 + 8u * s, 1);
+            mbar_init(d_empty0 + 8u * s, 16);  // 8 epilogue warps of each CTA (used in the leader only)
+        }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 2) {
+        asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)),
+                     "r"(512));
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::);
+    }
+    {
+        // the constant A tile of the norm K-step: columns 0-2 hold -0.5 (SWIZZLE_32B: chunk ^= (row >> 2) & 1)
+        float* ac = (float*)(smem + p.off_ac);
+#pragma unroll 1
+        for (int i = threadIdx.x; i < kRowsCta * 8; i += kGmThreads) {
+            const int row = i >> 3, col = i & 7;
+            const int phys = (col >> 2) ^ ((row >> 2) & 1);
+            ac[row * 8 + phys * 4 + (col & 3)] = col < 3 ? -0.5f : 0.f;
+        }
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // the tensor core reads it through the async proxy
+    }
+    tc_fence_before();
+    __syncthreads();
+    cluster_sync_all();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    const int n_sub = p.n_sub;
+    const int n_nt = p.n_ntiles;
+    const bool resident = p.resident != 0;
+
+    if (warp == 0) {
+        // ===================================== TMA producer =====================================
+        if (lane == 0) {
+            uint32_t a_seq = 0, b_seq = 0;
+            for (int64_t tile = cluster_id; tile < p.num_tiles; tile += n_clusters) {
+                const int row0 = (int)(tile * kRowsPair + rank * kRowsCta);
+                for (int nt = 0; nt < n_nt; ++nt) {
+                    const int brow = nt * N + (int)rank * halfN;
+                    for (int sc = 0; sc < n_sub; ++sc) {
+                        if ((sc & 1) == 0 && (!resident || nt == 0)) {
+                            const uint32_t s = a_seq % (uint32_t)NA;
+                            mbar_wait(a_empty0 + 8u * s, ((a_seq / (uint32_t)NA) & 1u) ^ 1u);
+                            mbar_arrive_expect_tx(a_full0 + 8u * s, (uint32_t)kASlotBytes);
+                            tma_load_2d(smem_base + p.off_a + s * kASlotBytes, &tmX, a_full0 + 8u * s, (sc >> 1) * 32, row0);
+                            ++a_seq;
+                        }
+                        const uint32_t s = b_seq % (uint32_t)NB;
+                        mbar_wait(b_empty0 + 8u * s, ((b_seq / (uint32_t)NB) & 1u) ^ 1u);
+                        mbar_arrive_expect_tx(b_full0 + 8u * s, (uint32_t)(2 * halfN * 64));
+                        const uint32_t dst = smem_base + p.off_b + s * p.b_slot_bytes;
+                        tma_load_2d(dst, &tmB, b_full0 + 8u * s, sc * 16, brow);
+                        tma_load_2d(dst + halfN * 64, &tmB, b_full0 + 8u * s, sc * 16, p.k_pad + brow);
+                        ++b_seq;
+                    }
+                    {  // the norm K-step of this N-tile
+                        const uint32_t s = b_seq % (uint32_t)NB;
+                        mbar_wait(b_empty0 + 8u * s, ((b_seq / (uint32_t)NB) & 1u) ^ 1u);
+                        mbar_arrive_expect_tx(b_full0 + 8u * s, (uint32_t)(halfN * 32));
+                        tma_load_2d(smem_base + p.off_b + s * p.b_slot_bytes, &tmCn, b_full0 + 8u * s, 0, brow);
+                        ++b_seq;
+                    }
+                }
+            }
+        }
+        __syncwarp();
+    } else if (warp == 1) {
+        // ================================ MMA issuer (leader) / relay (peer) ================================
+        // Leader: the whole warp runs the loop, one elected lane issues.  Peer: the same walk over the rings; as
+        // each of its slots lands it arrives on the leader's barrier of that slot.
+        const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(kRowsPair >> 4) << 24) |
+                               ((uint32_t)(N >> 3) << 17);
+        const uint64_t adesc0 = make_b_desc(smem_base + p.off_a, 128);
+        const uint64_t bdesc0 = make_b_desc(smem_base + p.off_b, 64);
+        const uint64_t cdesc0 = make_b_desc(smem_base + p.off_b, 32);
+        const uint64_t acdesc = make_b_desc(smem_base + p.off_ac, 32);
+        const uint64_t lo_off = (uint64_t)((halfN * 64) >> 4);
+        const uint32_t lead_a_full0 = map_to_cta(a_full0, 0), lead_b_full0 = map_to_cta(b_full0, 0);
+        uint32_t a_seq = 0, b_seq = 0, gnt = 0;
+        for (int64_t tile = cluster_id; tile < p.num_tiles; tile += n_clusters) {
+            for (int nt = 0; nt < n_nt; ++nt, ++gnt) {
+                const uint32_t buf = gnt & 1u;
+                const uint32_t d_tmem = tmem_base + buf * 256u;
+                if (rank == 0) {
+                    mbar_wait(d_empty0 + 8u * buf, ((gnt >> 1) & 1u) ^ 1u);
+                    tc_fence_after();
+                }
+                uint32_t aslot = 0;
+                for (int sc = 0; sc <= n_sub; ++sc) {
+                    const bool norm_step = sc == n_sub;
+                    if (!norm_step && (sc & 1) == 0) {
+                        if (!resident || nt == 0) {
+                            aslot = a_seq % (uint32_t)NA;
+                            mbar_wait(a_full0 + 8u * aslot, (a_seq / (uint32_t)NA) & 1u);
+                            if (rank != 0 && lane == 0) mbar_arrive_cluster(lead_a_full0 + 8u * aslot);
+                            ++a_seq;
+                        } else {
+                            aslot = (uint32_t)(sc >> 1);
+                        }
+                    }
+                    const uint32_t bslot = b_seq % (uint32_t)NB;
+                    mbar_wait(b_full0 + 8u * bslot, (b_seq / (uint32_t)NB) & 1u);
+                    if (rank != 0 && lane == 0) mbar_arrive_cluster(lead_b_full0 + 8u * bslot);
+                    ++b_seq;
+                    if (rank == 0) {
+                        tc_fence_after();
+                        if (elect_one()) {
+                            const uint64_t boff = (uint64_t)((bslot * (uint32_t)p.b_slot_bytes) >> 4);
+                            if (!norm_step) {
+                                // A: 64-byte half (sc & 1) of the 128-byte row, K-steps of 32 bytes
+                                const uint64_t ad = adesc0 + (uint64_t)((aslot * (uint32_t)kASlotBytes) >> 4) +
+                                                    (uint64_t)((sc & 1) * 4);
+                                const uint64_t bd = bdesc0 + boff;
+#pragma unroll
+                                for (int kk = 0; kk < 2; ++kk) {
+                                    mma_tf32_ss2(d_tmem, ad + 2 * kk, bd + 2 * kk, idesc, (sc | kk) != 0);
+                                    mma_tf32_ss2(d_tmem, ad + 2 * kk, bd + lo_off + 2 * kk, idesc, 1);
+                                }
+                                tc_commit_pair(b_empty0 + 8u * bslot);
+                                const bool a_done = ((sc & 1) == 1 || sc == n_sub - 1) && (!resident || nt == n_nt - 1);
+                                if (a_done) tc_commit_pair(a_empty0 + 8u * aslot);
+                            } else {
+                                mma_tf32_ss2(d_tmem, acdesc, cdesc0 + boff, idesc, 1);
+                                tc_commit_pair(b_empty0 + 8u * bslot);
+                                tc_commit_pair(d_full0 + 8u * buf);
+                            }
+                        }
+                        __syncwarp();
+                    }
+                }
+            }
+        }
+    } else if (warp >= kEpiWarp0) {
+        // ======================================= epilogue =======================================
+        const int q = warp & 3;  // TMEM lane quarter of this warp
+        const int half = (warp - kEpiWarp0) >> 2;
+        const int row = q * 32 + lane;
+        float* scr = (float*)(smem + p.off_scr);
+        const float cmax = p.st->cnorm_max;
+        const uint32_t my_d_empty0 = map_to_cta(d_empty0, 0);
+        uint32_t gnt = 0;
+        for (int64_t tile = cluster_id; tile < p.num_tiles; tile += n_clusters) {
+            const int64_t grow = tile * kRowsPair + rank * kRowsCta + row;
+            const bool valid = grow < p.n;
+            float xn = 0.f, xl = 0.f;
+            if (valid && half == 0) {  // consumed after the last N-tile
+                xn = p.xnorm[grow];
+                xl = p.xlo[grow];
+            }
+            float b1 = -FLT_MAX, b2 = -FLT_MAX, b3 = -FLT_MAX;
+            int cb1 = 0, cb2 = 0;
+            for (int nt = 0; nt < n_nt; ++nt, ++gnt) {
+                const uint32_t buf = gnt & 1u;
+                mbar_wait(d_full0 + 8u * buf, (gnt >> 1) & 1u);
+                tc_fence_after();
+                const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + buf * 256u + (uint32_t)(half * halfN);
+#pragma unroll 1
+                for (int c0 = 0; c0 < halfN; c0 += 32) {
+                    uint32_t sc[32];
+                    tmem_ld32(taddr + c0, sc);
+                    tmem_wait_ld();
+                    if (c0 + 32 >= halfN) {  // the scores of this N-tile are in registers: the buffer is free
+                        tc_fence_before();
+                        __syncwarp();
+                        if (lane == 0) mbar_arrive_cluster(my_d_empty0 + 8u * buf);
+                    }
+                    float key[32];
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) key[j] = __uint_as_float((sc[j] & ~31u) | (uint32_t)j);
+                    float t1, t2, t3;
+                    top3max_of_32(key, t1, t2, t3);
+                    const int col0 = nt * N + half * halfN + c0;
+                    merge3(b1, cb1, b2, cb2, b3, t1, col0, t2, col0, t3);
+                }
+            }
+            // ---- the two column halves of a row meet; half 0 decides ----
+            if (half == 1) {
+                scr[0 * kRowsCta + row] = b1;
+                scr[1 * kRowsCta + row] = __int_as_float(cb1);
+                scr[2 * kRowsCta + row] = b2;
+                scr[3 * kRowsCta + row] = __int_as_float(cb2);
+                scr[4 * kRowsCta + row] = b3;
+            }
+            named_bar_sync(1, 256);
+            if (half == 0) {
+                merge3(b1, cb1, b2, cb2, b3, scr[0 * kRowsCta + row], __float_as_int(scr[1 * kRowsCta + row]),
+                       scr[2 * kRowsCta + row], __float_as_int(scr[3 * kRowsCta + row]), scr[4 * kRowsCta + row]);
+                const int i1 = cb1 + (int)(__float_as_uint(b1) & 31u);
+                const int i2 = cb2 + (int)(__float_as_uint(b2) & 31u);
+                // D_j = ||x||^2 - 2 score_j; every quantity of the test is an upper bound (file header)
+                const float D1 = fmaf(-2.f, b1, xn), D2 = fmaf(-2.f, b2, xn), D3 = fmaf(-2.f, b3, xn);
+                const float scale = xn + cmax;
+                const float t = p.tol_x * sqrtf(xl);
+                const float eps = p.eps_rel * scale;
+                const float pad = p.abs_rel * scale;
+                const float r1 = sqrtf(fmaxf(D1, 0.f) + pad);
+                const float r2 = sqrtf(fmaxf(D2, 0.f) + pad);
+                const float r3 = sqrtf(fmaxf(D3, 0.f) + pad);
+                const bool open = valid && p.k > 1 && (D2 - D1) < 2.f * t * (r1 + r2) + eps;
+                const bool third = open && p.k > 2 && (D3 - D1) < 2.f * t * (r1 + r3) + eps;
+                if (valid) p.labels[grow] = i1;
+                const unsigned m = __ballot_sync(0xffffffffu, open);
+                if (m) {
+                    const int leader = __ffs(m) - 1;
+                    unsigned int base = 0;
+                    if (lane == leader) base = atomicAdd(p.open_count, (unsigned int)__popc(m));
+                    base = __shfl_sync(0xffffffffu, base, leader);
+                    if (open)
+                        p.open[base + __popc(m & ((1u << lane) - 1u))] =
+                            make_uint2((unsigned int)grow, (unsigned int)i2 | (third ? (1u << 24) : 0u));
+                }
+            }
+            named_bar_sync(2, 256);
+        }
+    }
+
+    tc_fence_before();
+    __syncthreads();
+    cluster_sync_all();
+    if (warp == 2) {
+        asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512));
+    }
+}
+
+// ---- host side ---------------------------------------------------------------------------------
+struct Plan {
+    int n_sub, n_chunks, d_pad, ntile, n_ntiles, k_pad, NA, NB, resident, b_slot_bytes;
+    int off_a, off_b, off_ac, off_scr, off_bar, total;
+    bool ok;
+};
+
+Plan make_plan(int d, int k) {
+    Plan pl = {};
+    pl.ok = false;
+    if (d <= 0 || k <= 0 || (d & 3) || k > (1 << 24) - 256) return pl;
+    pl.n_sub = (d + 15) / 16;
+    pl.n_chunks = (pl.n_sub + 1) / 2;
+    pl.d_pad = pl.n_sub * 16;
+    const int tiles = (k + 255) / 256;
+    const int per = (k + tiles - 1) / tiles;
+    pl.ntile = ((per + 63) / 64) * 64;
+    pl.n_ntiles = (k + pl.ntile - 1) / pl.ntile;
+    pl.k_pad = pl.n_ntiles * pl.ntile;
+    pl.b_slot_bytes = pl.ntile * 64;  // [hi: N/2 rows x 64 B | lo: N/2 rows x 64 B]
+    const int fixed = kConstABytes + kScrBytes + kBarBytes + 1024 /*alignment*/;
+    const int avail = kMaxSmem - fixed;
+    if (pl.n_chunks <= kMaxNA && pl.n_chunks * kASlotBytes + 4 * pl.b_slot_bytes <= avail) {
+        pl.resident = 1;
+        pl.NA = pl.n_chunks;
+    } else {
+        pl.resident = 0;
+        pl.NA = 4;
+    }
+    int nb = (avail - pl.NA * kASlotBytes) / pl.b_slot_bytes;
+    if (nb > kMaxNB) nb = kMaxNB;
+    if (nb < 2) return pl;
+    pl.NB = nb;
+    int off = 0;
+    pl.off_a = off;
+    off += pl.NA * kASlotBytes;
+    pl.off_b = off;
+    off += pl.NB * pl.b_slot_bytes;
+    off = (off + 1023) & ~1023;
+    pl.off_ac = off;
+    off += kConstABytes;
+    pl.off_scr = off;
+    off += kScrBytes;
+    pl.off_bar = off;
+    off += kBarBytes;
+    pl.total = off + 1024;
+    pl.ok = pl.total <= kMaxSmem;
+    return pl;
+}
+
+template <typename T>
+int grow_buf(T** p, size_t* cap, size_t need, const char* what) {
+    if (need <= *cap && *p) return 0;
+    if (*p) cudaFree(*p);
+    *p = nullptr;
+    *cap = 0;
+    const size_t want = need + need / 8 + 64;
+    if (cudaMalloc((void**)p, sizeof(T) * want) != cudaSuccess) {
+        snprintf(g_gm_err, sizeof(g_gm_err), "cudaMalloc of %zu bytes for %s failed", sizeof(T) * want, what);
+        return 1;
+    }
+    *cap = want;
+    return 0;
+}
+
+}  // namespace
+
+bool gemm_supported(const float* X, int d, int k) {
+    if ((reinterpret_cast<uintptr_t>(X) & 15) != 0) return false;
+    return make_plan(d, k).ok;
+}
+size_t gemm_workspace_bytes(int64_t n, int d, int k) {
+    const Plan pl = make_plan(d, k);
+    if (!pl.ok) return 0;
+    return sizeof(float) * (2 * (size_t)pl.k_pad * pl.d_pad + 8 * (size_t)pl.k_pad) + 8 * ((size_t)n + (size_t)n / 8 + 64) + 64;
+}
+const char* gemm_last_error() { return g_gm_err; }
+
+void gemm_free(GemmWorkspace* ws) {
+    if (ws->d_b) cudaFree(ws->d_b);
+    if (ws->d_cn) cudaFree(ws->d_cn);
+    if (ws->d_open) cudaFree(ws->d_open);
+    if (ws->d_count) cudaFree(ws->d_count);
+    *ws = GemmWorkspace();
+}
+
+void launch_rownorm2(const float* X, int64_t n, int d, float* xnorm, float* xlo, cudaStream_t s) {
+    if (n <= 0) return;
+    int64_t blocks = (n + 7) / 8;
+    if (blocks > kNumSMs * 16) blocks = kNumSMs * 16;
+    rownorm2_kernel<<<(unsigned)blocks, 256, 0, s>>>(X, n, d, xnorm, xlo);
+    count_launch();
+}
+
+void launch_rowdist(const float* X, int64_t n, int d, const float* C, const int32_t* labels, float* best,
+                    cudaStream_t s) {
+    if (n <= 0) return;
+    int64_t blocks = (n + 7) / 8;
+    if (blocks > kNumSMs * 16) blocks = kNumSMs * 16;
+    rowdist_kernel<<<(unsigned)blocks, 256, 0, s>>>(X, n, d, C, labels, best);
+    count_launch();
+}
+
+int gemm_pass(GemmWorkspace* ws, const float* X, int64_t n, int d, int k, const float* C, const float* cnorm,
+              const float* xnorm, const float* xlo, int32_t* labels, IterState* st, bool honor_done, cudaStream_t s) {
+    const Plan pl = make_plan(d, k);
+    if (!pl.ok) {
+        snprintf(g_gm_err, sizeof(g_gm_err), "shape d=%d k=%d does not fit the tcgen05 tile-GEMM kernel (needs d %% 4 == 0)", d, k);
+        return 1;
+    }
+    if (n <= 0) return 0;
+    if (grow_buf((float**)&ws->d_b, &ws->b_cap, 2 * (size_t)pl.k_pad * pl.d_pad, "the TF32 centroids")) return 1;
+    if (grow_buf((float**)&ws->d_cn, &ws->cn_cap, 8 * (size_t)pl.k_pad, "the centroid norms")) return 1;
+    if (grow_buf((uint2**)&ws->d_open, &ws->open_cap, (size_t)n, "the open-row list")) return 1;
+    if (!ws->d_count && cudaMalloc((void**)&ws->d_count, 64) != cudaSuccess) {
+        snprintf(g_gm_err, sizeof(g_gm_err), "cudaMalloc of the open-row counter failed");
+        return 1;
+    }
+    CUtensorMap tmX, tmB, tmCn;
+    char* e = g_gm_err;
+    const size_t el = sizeof(g_gm_err);
+    if (encode_2d(e, el, &tmX, X, (uint64_t)d, (uint64_t)n, (uint64_t)d * 4, 32, kRowsCta)) return 1;
+    if (encode_2d(e, el, &tmB, ws->d_b, (uint64_t)pl.d_pad, (uint64_t)2 * pl.k_pad, (uint64_t)pl.d_pad * 4, 16,
+                  (uint32_t)(pl.ntile / 2)))
+        return 1;
+    if (encode_2d(e, el, &tmCn, ws->d_cn, 8, (uint64_t)pl.k_pad, 32, 8, (uint32_t)(pl.ntile / 2))) return 1;
+
+    static PerDeviceOnce attr_set;  // the opt-in is a per-device attribute
+    const int dev = PerDeviceOnce::current();
+    if (dev < 0 || !attr_set.done[dev]) {
+        if (cudaFuncSetAttribute(kmeans_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxSmem) != cudaSuccess) {
+            snprintf(g_gm_err, sizeof(g_gm_err), "cannot raise dynamic shared memory to %d bytes", kMaxSmem);
+            return 1;
+        }
+        if (dev >= 0) attr_set.done[dev] = true;
+    }
+    {
+        const size_t total = (size_t)pl.k_pad * pl.d_pad;
+        size_t blocks = (total + 255) / 256;
+        if (blocks > (size_t)kNumSMs * 8) blocks = (size_t)kNumSMs * 8;
+        gemm_prep_kernel<<<(unsigned)blocks, 256, 0, s>>>(C, cnorm, k, d, pl.k_pad, pl.d_pad, (float*)ws->d_b,
+                                                         (float*)ws->d_cn);
+        count_launch();
+    }
+    cudaMemsetAsync(ws->d_count, 0, sizeof(unsigned int), s);
+
+    GmParams p;
+    p.n = n;
+    p.num_tiles = (n + kRowsPair - 1) / kRowsPair;
+    p.d = d;
+    p.k = k;
+    p.k_pad = pl.k_pad;
+    p.n_sub = pl.n_sub;
+    p.ntile = pl.ntile;
+    p.n_ntiles = pl.n_ntiles;
+    p.NA = pl.NA;
+    p.NB = pl.NB;
+    p.resident = pl.resident;
+    p.b_slot_bytes = pl.b_slot_bytes;
+    p.xnorm = xnorm;
+    p.xlo = xlo;
+    p.labels = labels;
+    p.open = (uint2*)ws->d_open;
+    p.open_count = (unsigned int*)ws->d_count;
+    p.st = st;
+    p.honor_done = honor_done ? 1 : 0;
+    // Error model (file header; the same as kernels_screen.cu).  x is read truncated to TF32, ||x - x^|| is the
+    // row's own measured value (tol_x = slack of its FP32 evaluation) and <= 2^-10 ||x|| (abs_rel).  The rest is
+    // FP32 rounding: the tensor core adds every MMA's products into the accumulator with truncation (<= 1 ulp of
+    // the running sum per MMA, 2 ceil(d/8) + 1 MMAs), the c_hi / c_lo split leaves 2^-22 |c|, ||x||^2 rounds
+    // once, and the index packed into the 5 low mantissa bits moves a score by < 2^-18 of itself.  With
+    // 2 |x||c| <= |x|^2 + |c|^2 a margin carries at most eps_rel (||x||^2 + max ||c||^2) of all that.
+    p.tol_x = 1.002f;
+    p.eps_rel = 2.f * (float)(2 * ((d + 7) / 8) + 8) * 1.1920928955078125e-07f + 1e-6f + 1.6e-5f;
+    p.abs_rel = 9.765625e-4f * 1.001f + p.eps_rel;
+    p.off_a = pl.off_a;
+    p.off_b = pl.off_b;
+    p.off_ac = pl.off_ac;
+    p.off_scr = pl.off_scr;
+    p.off_bar = pl.off_bar;
+    int64_t clusters = p.num_tiles < kNumSMs / 2 ? p.num_tiles : kNumSMs / 2;
+    if (clusters < 1) clusters = 1;
+    kmeans_gemm_kernel<<<(unsigned)(2 * clusters), kGmThreads, pl.total, s>>>(tmX, tmB, tmCn, p);
+    count_launch();
+    cudaError_t err = cudaGetLastError();
+    if (err != cudaSuccess) {
+        snprintf(g_gm_err, sizeof(g_gm_err), "tile-GEMM kernel launch failed: %s", cudaGetErrorString(err));
+        return 1;
+    }
+    {
+        int64_t blocks = (n + 7) / 8;
+        if (blocks > kNumSMs * 8) blocks = kNumSMs * 8;
+        gemm_fixup_kernel<<<(unsigned)blocks, 256, 0, s>>>(X, d, k, C, (const uint2*)ws->d_open,
+                                                          (const unsigned int*)ws->d_count, labels, st, honor_done ? 1 : 0);
+        count_launch();
+    }
+    return 0;
+}
+
+}  // namespace b200km

@@ -40,4 +40,28 @@ void screen_inertia_fix(const float* C, int k, int d, double* acc, cudaStream_t 
 const char* screen_last_error();
 void tc_free(TcWorkspace* ws);
 
+// Tile-GEMM kernel (kernels_gemm.cu): nearest centroid for any k and any d % 4 == 0 on a CTA pair
+// (tcgen05.mma.cta_group::2), centroids streamed in N-tiles, exact labels through a fix-up list.
+struct GemmWorkspace {
+    void* d_b = nullptr;  // [2*k_pad][d_pad] TF32 split of the centroids
+    size_t b_cap = 0;
+    void* d_cn = nullptr;  // [k_pad][8] three-term TF32 split of ||c||^2
+    size_t cn_cap = 0;
+    void* d_open = nullptr;  // (row, runner-up | mode) of the rows the TF32 scores did not decide
+    size_t open_cap = 0;
+    void* d_count = nullptr;
+};
+bool gemm_supported(const float* X, int d, int k);
+size_t gemm_workspace_bytes(int64_t n, int d, int k);
+// labels[n] (required): exact nearest centroid of every row once the stream reaches this point.
+// xnorm / xlo: ||x||^2 and ||x - trunc_tf32(x)||^2 per row (launch_rownorm2).
+int gemm_pass(GemmWorkspace* ws, const float* X, int64_t n, int d, int k, const float* C, const float* cnorm,
+              const float* xnorm, const float* xlo, int32_t* labels, IterState* st, bool honor_done, cudaStream_t s);
+void launch_rownorm2(const float* X, int64_t n, int d, float* xnorm, float* xlo, cudaStream_t s);
+// best[i] = ||x_i - c_labels[i]||^2 from FP32 differences
+void launch_rowdist(const float* X, int64_t n, int d, const float* C, const int32_t* labels, float* best,
+                    cudaStream_t s);
+const char* gemm_last_error();
+void gemm_free(GemmWorkspace* ws);
+
 }  // namespace b200km
