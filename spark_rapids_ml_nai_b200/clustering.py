@@ -209,9 +209,23 @@ class _DevicePredictor:
         labels, _ = self.handle.predict(X, self.centers)
         return labels.cpu().numpy()
 
+    def predict_many(self, batches: List[np.ndarray]) -> np.ndarray:
+        """Labels of several host batches at once: one packed host -> device copy, one pass, one read-back."""
+        batches = [b for b in batches if b.shape[0]]
+        if not batches:
+            return np.empty(0, dtype=np.int32)
+        X = partitions_to_device(list(batches), self.device, free_inputs=False)
+        labels, _ = self.handle.predict(X, self.centers)
+        return labels.cpu().numpy()
+
+    def close(self) -> None:
+        if self.handle is not None:
+            self.handle.destroy()
+            self.handle = None
+
     def __del__(self) -> None:
         try:
-            self.handle.destroy()
+            self.close()
         except Exception:
             pass
 

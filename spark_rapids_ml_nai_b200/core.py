@@ -29,6 +29,26 @@ param_alias = namedtuple("ParamAlias", ("cuml_init", "handle", "num_cols", "part
 alias = namedtuple("Alias", ("data", "label", "row_number"))("cuml_values", "cuml_label", "unique_id")
 
 FitInputType = List[Tuple[Any, Optional[Any], Optional[Any]]]
+_TRANSFORM_COALESCE_ROWS = 1 << 20
+
+
+def _batch_features(pdf: pd.DataFrame, input_col: Optional[str], multi_col_names: Optional[List[str]],
+                    order: str, dtype: Any) -> np.ndarray:
+    """One Arrow-sized batch -> dense [rows, d] array (reference core.py:727-733 and :1549-1551).
+
+    Multi-column numeric input whose columns are the whole frame, in order, in one block of the right dtype is
+    taken as a view (no copy: the loader copies it once, into pinned memory); an array column is stacked row
+    by row, as the reference does."""
+    if multi_col_names:
+        if list(pdf.columns) == list(multi_col_names):
+            a = pdf.to_numpy(copy=False)
+            if a.dtype == dtype and (a.flags["C_CONTIGUOUS"] if order == "C" else a.flags["F_CONTIGUOUS"]):
+                return a
+        return np.array(pdf[multi_col_names], order=order, dtype=dtype)
+    col = pdf[input_col]
+    if len(col) and isinstance(col.iloc[0], np.ndarray) and col.iloc[0].dtype == dtype:
+        return np.stack(col.to_numpy()).astype(dtype, order=order, copy=False)
+    return np.array(list(col), order=order, dtype=dtype)
 
 
 # ---- persistence: the on-disk layout of pyspark's DefaultParamsWriter + one JSON line of attributes ----
@@ -180,11 +200,7 @@ class _CumlCaller(_CumlParams, _CumlCommon):
             sizes: List[int] = []
             for pdf in pdf_iter:
                 sizes.append(pdf.shape[0])
-                if multi_col_names:
-                    features = np.array(pdf[multi_col_names], order=array_order, dtype=dtype)
-                else:
-                    features = np.array(list(pdf[input_col]), order=array_order, dtype=dtype)
-                inputs.append((features, None, None))
+                inputs.append((_batch_features(pdf, input_col, multi_col_names, array_order, dtype), None, None))
             if len(sizes) == 0 or all(sz == 0 for sz in sizes):
                 raise RuntimeError(
                     "A python worker received no data.  Please increase amount of data or use fewer workers."
@@ -297,12 +313,32 @@ class _CumlModel(_CumlParams, _CumlCommon):
             _CumlCommon._set_gpu_device(BarrierTaskContext(pid, dataset.getNumPartitions(), False), is_transform=True)
             backend = construct()
             series: List[pd.Series] = []
-            for pdf in dataset.batches(pid):
-                if input_cols is not None:
-                    data = np.array(pdf[input_cols], order=array_order, dtype=dtype)
-                else:
-                    data = np.array(list(pdf[input_col]), order=array_order, dtype=dtype)
-                series.append(transform_fn(backend, data))
+            # Arrow-sized batches (10 000 rows by default) are far too small for one device round trip each:
+            # a backend that offers `predict_many` gets them coalesced into >= _TRANSFORM_COALESCE_ROWS rows
+            # (one packed host -> device copy, one kernel pass, one device -> host read per group)
+            pending: List[np.ndarray] = []
+            pending_rows = 0
+
+            def drain() -> None:
+                nonlocal pending, pending_rows
+                if pending:
+                    series.append(pd.Series(backend.predict_many(pending)))
+                    pending, pending_rows = [], 0
+
+            try:
+                for pdf in dataset.batches(pid):
+                    data = _batch_features(pdf, input_col, input_cols, array_order, dtype)
+                    if hasattr(backend, "predict_many"):
+                        pending.append(data)
+                        pending_rows += data.shape[0]
+                        if pending_rows >= _TRANSFORM_COALESCE_ROWS:
+                            drain()
+                    else:
+                        series.append(transform_fn(backend, data))
+                drain()
+            finally:
+                if hasattr(backend, "close"):
+                    backend.close()  # the task owns the backend object: release its device handle now
             part = dataset.partitions[pid].copy()
             part[pred_col] = (pd.concat(series, ignore_index=True) if series else pd.Series([], dtype="int32")).to_numpy()
             out_parts.append(part)

@@ -32,6 +32,7 @@
 #include <cfloat>
 #include <climits>
 #include <cstdio>
+#include <cstdlib>
 
 namespace b200km {
 
@@ -62,6 +63,8 @@ struct GmParams {
     int n_ntiles;  // k_pad / ntile
     int NA, NB, resident;
     int b_slot_bytes;
+    const float* bt;   // pre-tiled B operand (gemm_prep_kernel)
+    const float* cnt;  // pre-tiled norm operand
     const float* xnorm;
     const float* xlo;
     int32_t* labels;
@@ -71,6 +74,7 @@ struct GmParams {
     int honor_done;
     float tol_x, eps_rel, abs_rel;
     int off_a, off_b, off_ac, off_scr, off_bar;
+    unsigned long long* trace;  // development aid (B200KM_ENABLE_TRACE builds): [16 roles][1024] clock64 of cluster 0
 };
 
 // ---- cluster / cta_group::2 PTX ------------------------------------------------------------------
@@ -109,6 +113,28 @@ __device__ __forceinline__ void mma_tf32_ss2(uint32_t d_tmem, uint64_t a_desc, u
         "}" ::"r"(d_tmem),
         "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
         : "memory");
+}
+__device__ __forceinline__ void gtrace(const GmParams& p, int role, uint32_t idx) {
+#ifdef B200KM_ENABLE_TRACE
+    if (p.trace && blockIdx.x < 2 && idx < 1024u) p.trace[(role + (blockIdx.x ? 8 : 0)) * 1024 + idx] = (unsigned long long)clock64();
+#endif
+}
+// Position in a ring of `n` slots, advanced without divisions: the single-thread roles of this kernel run at the
+// latency of their dependent instructions, and one 32-bit division costs more than an MMA.
+struct RingPos {
+    uint32_t slot = 0, phase = 0;
+    __device__ __forceinline__ void next(uint32_t n) {
+        if (++slot == n) {
+            slot = 0;
+            phase ^= 1u;
+        }
+    }
+};
+// contiguous global -> shared bulk copy, completion counted on an mbarrier
+__device__ __forceinline__ void bulk_load(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst),
+                 "l"(src), "r"(bytes), "r"(bar)
+                 : "memory");
 }
 __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&r)[32]) {
     asm volatile(
@@ -175,33 +201,47 @@ __device__ __forceinline__ void merge3(float& b1, int& cb1, float& b2, int& cb2,
 }
 
 // ------------------------------------------------------------------------------------------------
-// Operand preparation of a pass.  bsplit[2*k_pad][d_pad]: rows [0,k_pad) = centroids rounded to TF32, rows
-// [k_pad, 2k_pad) = the TF32-rounded remainders, zero padded.  cn3[k_pad][8]: columns 0-2 = three-term TF32 split
-// of ||c_j||^2 (kCnPad for padded rows), columns 3-7 zero.
+// Operand preparation of a pass: the B operand in exactly the bytes the tensor core reads from shared memory, so
+// that a ring slot is one contiguous bulk copy (a 2-D TMA box of 64-byte rows costs the TMA unit one request per
+// row: measured ~1700 cycles per 16 KB slot, three times the slot's MMA time).
+//   bt: blocks [(nt*2 + rank) * n_sub + sc] of N*16 floats = [hi: N/2 rows x 16 floats | lo: same], rows =
+//       centroids nt*N + rank*N/2 + row, columns sc*16 .., SWIZZLE_64B (16-byte chunk ^= (row >> 1) & 3);
+//       hi = centroid rounded to TF32, lo = the TF32-rounded remainder, zero padded.
+//   cnt: blocks [nt*2 + rank] of N/2 rows x 8 floats, SWIZZLE_32B (chunk ^= (row >> 2) & 1): columns 0-2 = the
+//       three-term TF32 split of ||c_j||^2 (kCnPad for padded rows), the rest zero.
 __global__ void __launch_bounds__(256) gemm_prep_kernel(const float* __restrict__ C, const float* __restrict__ cnorm,
-                                                        int k, int d, int k_pad, int d_pad, float* __restrict__ bsplit,
-                                                        float* __restrict__ cn3) {
-    const size_t total = (size_t)k_pad * d_pad;
+                                                        int k, int d, int k_pad, int n_sub, int halfN,
+                                                        float* __restrict__ bt, float* __restrict__ cnt) {
+    const size_t total = (size_t)k_pad * n_sub * 16;
     const size_t stride = (size_t)gridDim.x * blockDim.x;
-    for (size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += stride) {
-        const int j = (int)(idx / d_pad), i = (int)(idx - (size_t)j * d_pad);
+    const int part = halfN * 16;  // floats of one block's hi part
+    for (size_t o = (size_t)blockIdx.x * blockDim.x + threadIdx.x; o < total; o += stride) {
+        const size_t b = o / part;
+        const int r = (int)(o - b * part);
+        const int row = r >> 4, pc = (r >> 2) & 3, w = r & 3;
+        const int col = ((pc ^ ((row >> 1) & 3)) << 2) | w;
+        const int sc = (int)(b % n_sub);
+        const size_t j = (b / n_sub) * halfN + row;
+        const int i = sc * 16 + col;
         float hi = 0.f, lo = 0.f;
-        if (j < k && i < d) {
-            const float c = C[(size_t)j * d + i];
+        if (j < (size_t)k && i < d) {
+            const float c = C[j * d + i];
             hi = __uint_as_float(tf32_round(__float_as_uint(c)));
             lo = __uint_as_float(tf32_round(__float_as_uint(c - hi)));
         }
-        bsplit[idx] = hi;
-        bsplit[total + idx] = lo;
+        bt[b * 2 * part + r] = hi;
+        bt[b * 2 * part + part + r] = lo;
     }
     for (size_t j = (size_t)blockIdx.x * blockDim.x + threadIdx.x; j < (size_t)k_pad; j += stride) {
         const float v = j < (size_t)k ? cnorm[j] : kCnPad;
         const float a = __uint_as_float(tf32_round(__float_as_uint(v)));
         const float b = __uint_as_float(tf32_round(__float_as_uint(v - a)));
         const float c = __uint_as_float(tf32_round(__float_as_uint((v - a) - b)));
-        float4* o = reinterpret_cast<float4*>(cn3 + j * 8);
-        o[0] = make_float4(a, b, c, 0.f);
-        o[1] = make_float4(0.f, 0.f, 0.f, 0.f);
+        const int row = (int)(j % halfN);
+        const int swz = (row >> 2) & 1;
+        float4* o = reinterpret_cast<float4*>(cnt + j * 8);
+        o[swz] = make_float4(a, b, c, 0.f);
+        o[swz ^ 1] = make_float4(0.f, 0.f, 0.f, 0.f);
     }
 }
 
@@ -342,8 +382,7 @@ __global__ void __launch_bounds__(256) rowdist_kernel(const float* __restrict__ 
 
 // ------------------------------------------------------------------------------------------------
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kGmThreads, 1)
-    kmeans_gemm_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ CUtensorMap tmB,
-                       const __grid_constant__ CUtensorMap tmCn, const GmParams p) {
+    kmeans_gemm_kernel(const __grid_constant__ CUtensorMap tmX, const GmParams p) {
     if (p.honor_done && p.st->done) return;  // both CTAs of a pair read the same flag
 
     extern __shared__ __align__(1024) uint8_t smem_raw[];
@@ -407,38 +446,47 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kGmThreads, 1)
     const int n_sub = p.n_sub;
     const int n_nt = p.n_ntiles;
     const bool resident = p.resident != 0;
+    // Every cluster walks the N-tiles and the K sub-chunks of B in its own rotation: with all clusters in step,
+    // the whole chip would ask the same few L2 slices for the same B lines at the same time.
+    const int nt0 = (int)(cluster_id % n_nt);
+    const int sc0 = 2 * (int)((cluster_id / n_nt) % ((n_sub + 1) / 2));  // whole A chunks: even
 
     if (warp == 0) {
         // ===================================== TMA producer =====================================
         if (lane == 0) {
-            uint32_t a_seq = 0, b_seq = 0;
+            RingPos ar, br;
+            const size_t blk = (size_t)N * 16;  // floats of one B block
             for (int64_t tile = cluster_id; tile < p.num_tiles; tile += n_clusters) {
                 const int row0 = (int)(tile * kRowsPair + rank * kRowsCta);
-                for (int nt = 0; nt < n_nt; ++nt) {
-                    const int brow = nt * N + (int)rank * halfN;
-                    for (int sc = 0; sc < n_sub; ++sc) {
-                        if ((sc & 1) == 0 && (!resident || nt == 0)) {
-                            const uint32_t s = a_seq % (uint32_t)NA;
-                            mbar_wait(a_empty0 + 8u * s, ((a_seq / (uint32_t)NA) & 1u) ^ 1u);
-                            mbar_arrive_expect_tx(a_full0 + 8u * s, (uint32_t)kASlotBytes);
-                            tma_load_2d(smem_base + p.off_a + s * kASlotBytes, &tmX, a_full0 + 8u * s, (sc >> 1) * 32, row0);
-                            ++a_seq;
+                int nt = nt0;
+                for (int nti = 0; nti < n_nt; ++nti) {
+                    const float* bt_nt = p.bt + (size_t)(nt * 2 + (int)rank) * (size_t)n_sub * blk;
+                    int sc = sc0;
+                    for (int sci = 0; sci < n_sub; ++sci) {
+                        if ((sc & 1) == 0 && (!resident || nti == 0)) {  // first touch of this A chunk
+                            mbar_wait(a_empty0 + 8u * ar.slot, ar.phase ^ 1u);
+                            mbar_arrive_expect_tx(a_full0 + 8u * ar.slot, (uint32_t)kASlotBytes);
+                            tma_load_2d(smem_base + p.off_a + ar.slot * kASlotBytes, &tmX, a_full0 + 8u * ar.slot,
+                                        (sc >> 1) * 32, row0);
+                            ar.next((uint32_t)NA);
                         }
-                        const uint32_t s = b_seq % (uint32_t)NB;
-                        mbar_wait(b_empty0 + 8u * s, ((b_seq / (uint32_t)NB) & 1u) ^ 1u);
-                        mbar_arrive_expect_tx(b_full0 + 8u * s, (uint32_t)(2 * halfN * 64));
-                        const uint32_t dst = smem_base + p.off_b + s * p.b_slot_bytes;
-                        tma_load_2d(dst, &tmB, b_full0 + 8u * s, sc * 16, brow);
-                        tma_load_2d(dst + halfN * 64, &tmB, b_full0 + 8u * s, sc * 16, p.k_pad + brow);
-                        ++b_seq;
+                        mbar_wait(b_empty0 + 8u * br.slot, br.phase ^ 1u);
+                        gtrace(p, 0, (uint32_t)sci);
+                        mbar_arrive_expect_tx(b_full0 + 8u * br.slot, (uint32_t)p.b_slot_bytes);
+                        bulk_load(smem_base + p.off_b + br.slot * p.b_slot_bytes, bt_nt + (size_t)sc * blk,
+                                  (uint32_t)p.b_slot_bytes, b_full0 + 8u * br.slot);
+                        br.next((uint32_t)NB);
+                        if (++sc == n_sub) sc = 0;
                     }
                     {  // the norm K-step of this N-tile
-                        const uint32_t s = b_seq % (uint32_t)NB;
-                        mbar_wait(b_empty0 + 8u * s, ((b_seq / (uint32_t)NB) & 1u) ^ 1u);
-                        mbar_arrive_expect_tx(b_full0 + 8u * s, (uint32_t)(halfN * 32));
-                        tma_load_2d(smem_base + p.off_b + s * p.b_slot_bytes, &tmCn, b_full0 + 8u * s, 0, brow);
-                        ++b_seq;
+                        mbar_wait(b_empty0 + 8u * br.slot, br.phase ^ 1u);
+                        mbar_arrive_expect_tx(b_full0 + 8u * br.slot, (uint32_t)(halfN * 32));
+                        bulk_load(smem_base + p.off_b + br.slot * p.b_slot_bytes,
+                                  p.cnt + (size_t)(nt * 2 + (int)rank) * (size_t)(halfN * 8), (uint32_t)(halfN * 32),
+                                  b_full0 + 8u * br.slot);
+                        br.next((uint32_t)NB);
                     }
+                    if (++nt == n_nt) nt = 0;
                 }
             }
         }
@@ -454,55 +502,67 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kGmThreads, 1)
         const uint64_t cdesc0 = make_b_desc(smem_base + p.off_b, 32);
         const uint64_t acdesc = make_b_desc(smem_base + p.off_ac, 32);
         const uint64_t lo_off = (uint64_t)((halfN * 64) >> 4);
+        const uint32_t b_slot16 = (uint32_t)p.b_slot_bytes >> 4;
         const uint32_t lead_a_full0 = map_to_cta(a_full0, 0), lead_b_full0 = map_to_cta(b_full0, 0);
-        uint32_t a_seq = 0, b_seq = 0, gnt = 0;
+        RingPos ar, br;
+        uint32_t gnt = 0;
         for (int64_t tile = cluster_id; tile < p.num_tiles; tile += n_clusters) {
-            for (int nt = 0; nt < n_nt; ++nt, ++gnt) {
+            for (int nti = 0; nti < n_nt; ++nti, ++gnt) {
                 const uint32_t buf = gnt & 1u;
                 const uint32_t d_tmem = tmem_base + buf * 256u;
                 if (rank == 0) {
                     mbar_wait(d_empty0 + 8u * buf, ((gnt >> 1) & 1u) ^ 1u);
                     tc_fence_after();
                 }
-                uint32_t aslot = 0;
-                for (int sc = 0; sc <= n_sub; ++sc) {
-                    const bool norm_step = sc == n_sub;
-                    if (!norm_step && (sc & 1) == 0) {
-                        if (!resident || nt == 0) {
-                            aslot = a_seq % (uint32_t)NA;
-                            mbar_wait(a_full0 + 8u * aslot, (a_seq / (uint32_t)NA) & 1u);
+                uint32_t aslot = 0, a_idx = 0;
+                int sc = sc0;
+                for (int sci = 0; sci < n_sub; ++sci) {
+                    if ((sc & 1) == 0) {
+                        if (!resident || nti == 0) {
+                            aslot = ar.slot;
+                            mbar_wait(a_full0 + 8u * aslot, ar.phase);
                             if (rank != 0 && lane == 0) mbar_arrive_cluster(lead_a_full0 + 8u * aslot);
-                            ++a_seq;
+                            ar.next((uint32_t)NA);
                         } else {
-                            aslot = (uint32_t)(sc >> 1);
+                            aslot = a_idx;  // resident: the chunks sit in the slots in this cluster's load order
                         }
+                        ++a_idx;
                     }
-                    const uint32_t bslot = b_seq % (uint32_t)NB;
-                    mbar_wait(b_full0 + 8u * bslot, (b_seq / (uint32_t)NB) & 1u);
+                    const uint32_t bslot = br.slot;
+                    mbar_wait(b_full0 + 8u * bslot, br.phase);
                     if (rank != 0 && lane == 0) mbar_arrive_cluster(lead_b_full0 + 8u * bslot);
-                    ++b_seq;
+                    br.next((uint32_t)NB);
+                    if (rank == 0) {
+                        tc_fence_after();
+                        if (lane == 0) gtrace(p, 1, (uint32_t)sci);
+                        if (elect_one()) {
+                            // A: 64-byte half (sc & 1) of the 128-byte row, K-steps of 32 bytes
+                            const uint64_t ad = adesc0 + (uint64_t)((aslot << 10) + (uint32_t)((sc & 1) * 4));
+                            const uint64_t bd = bdesc0 + (uint64_t)(bslot * b_slot16);
+#pragma unroll
+                            for (int kk = 0; kk < 2; ++kk) {
+                                mma_tf32_ss2(d_tmem, ad + 2 * kk, bd + 2 * kk, idesc, (sci | kk) != 0);
+                                mma_tf32_ss2(d_tmem, ad + 2 * kk, bd + lo_off + 2 * kk, idesc, 1);
+                            }
+                            tc_commit_pair(b_empty0 + 8u * bslot);
+                            const bool a_done = ((sc & 1) == 1 || sc == n_sub - 1) && (!resident || nti == n_nt - 1);
+                            if (a_done) tc_commit_pair(a_empty0 + 8u * aslot);
+                        }
+                        __syncwarp();
+                    }
+                    if (++sc == n_sub) sc = 0;
+                }
+                {  // the norm K-step closes the N-tile
+                    const uint32_t bslot = br.slot;
+                    mbar_wait(b_full0 + 8u * bslot, br.phase);
+                    if (rank != 0 && lane == 0) mbar_arrive_cluster(lead_b_full0 + 8u * bslot);
+                    br.next((uint32_t)NB);
                     if (rank == 0) {
                         tc_fence_after();
                         if (elect_one()) {
-                            const uint64_t boff = (uint64_t)((bslot * (uint32_t)p.b_slot_bytes) >> 4);
-                            if (!norm_step) {
-                                // A: 64-byte half (sc & 1) of the 128-byte row, K-steps of 32 bytes
-                                const uint64_t ad = adesc0 + (uint64_t)((aslot * (uint32_t)kASlotBytes) >> 4) +
-                                                    (uint64_t)((sc & 1) * 4);
-                                const uint64_t bd = bdesc0 + boff;
-#pragma unroll
-                                for (int kk = 0; kk < 2; ++kk) {
-                                    mma_tf32_ss2(d_tmem, ad + 2 * kk, bd + 2 * kk, idesc, (sc | kk) != 0);
-                                    mma_tf32_ss2(d_tmem, ad + 2 * kk, bd + lo_off + 2 * kk, idesc, 1);
-                                }
-                                tc_commit_pair(b_empty0 + 8u * bslot);
-                                const bool a_done = ((sc & 1) == 1 || sc == n_sub - 1) && (!resident || nt == n_nt - 1);
-                                if (a_done) tc_commit_pair(a_empty0 + 8u * aslot);
-                            } else {
-                                mma_tf32_ss2(d_tmem, acdesc, cdesc0 + boff, idesc, 1);
-                                tc_commit_pair(b_empty0 + 8u * bslot);
-                                tc_commit_pair(d_full0 + 8u * buf);
-                            }
+                            mma_tf32_ss2(d_tmem, acdesc, cdesc0 + (uint64_t)(bslot * b_slot16), idesc, 1);
+                            tc_commit_pair(b_empty0 + 8u * bslot);
+                            tc_commit_pair(d_full0 + 8u * buf);
                         }
                         __syncwarp();
                     }
@@ -528,10 +588,13 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kGmThreads, 1)
             }
             float b1 = -FLT_MAX, b2 = -FLT_MAX, b3 = -FLT_MAX;
             int cb1 = 0, cb2 = 0;
-            for (int nt = 0; nt < n_nt; ++nt, ++gnt) {
+            int nt = nt0;
+            for (int nti = 0; nti < n_nt; ++nti, ++gnt) {
                 const uint32_t buf = gnt & 1u;
                 mbar_wait(d_full0 + 8u * buf, (gnt >> 1) & 1u);
                 tc_fence_after();
+                if (warp == kEpiWarp0 && lane == 0) gtrace(p, 4, gnt * 2);
+
                 const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + buf * 256u + (uint32_t)(half * halfN);
 #pragma unroll 1
                 for (int c0 = 0; c0 < halfN; c0 += 32) {
@@ -551,6 +614,8 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kGmThreads, 1)
                     const int col0 = nt * N + half * halfN + c0;
                     merge3(b1, cb1, b2, cb2, b3, t1, col0, t2, col0, t3);
                 }
+                if (warp == kEpiWarp0 && lane == 0) gtrace(p, 4, gnt * 2 + 1);
+                if (++nt == n_nt) nt = 0;
             }
             // ---- the two column halves of a row meet; half 0 decides ----
             if (half == 1) {
@@ -719,14 +784,8 @@ int gemm_pass(GemmWorkspace* ws, const float* X, int64_t n, int d, int k, const 
         snprintf(g_gm_err, sizeof(g_gm_err), "cudaMalloc of the open-row counter failed");
         return 1;
     }
-    CUtensorMap tmX, tmB, tmCn;
-    char* e = g_gm_err;
-    const size_t el = sizeof(g_gm_err);
-    if (encode_2d(e, el, &tmX, X, (uint64_t)d, (uint64_t)n, (uint64_t)d * 4, 32, kRowsCta)) return 1;
-    if (encode_2d(e, el, &tmB, ws->d_b, (uint64_t)pl.d_pad, (uint64_t)2 * pl.k_pad, (uint64_t)pl.d_pad * 4, 16,
-                  (uint32_t)(pl.ntile / 2)))
-        return 1;
-    if (encode_2d(e, el, &tmCn, ws->d_cn, 8, (uint64_t)pl.k_pad, 32, 8, (uint32_t)(pl.ntile / 2))) return 1;
+    CUtensorMap tmX;
+    if (encode_2d(g_gm_err, sizeof(g_gm_err), &tmX, X, (uint64_t)d, (uint64_t)n, (uint64_t)d * 4, 32, kRowsCta)) return 1;
 
     static PerDeviceOnce attr_set;  // the opt-in is a per-device attribute
     const int dev = PerDeviceOnce::current();
@@ -741,8 +800,8 @@ int gemm_pass(GemmWorkspace* ws, const float* X, int64_t n, int d, int k, const 
         const size_t total = (size_t)pl.k_pad * pl.d_pad;
         size_t blocks = (total + 255) / 256;
         if (blocks > (size_t)kNumSMs * 8) blocks = (size_t)kNumSMs * 8;
-        gemm_prep_kernel<<<(unsigned)blocks, 256, 0, s>>>(C, cnorm, k, d, pl.k_pad, pl.d_pad, (float*)ws->d_b,
-                                                         (float*)ws->d_cn);
+        gemm_prep_kernel<<<(unsigned)blocks, 256, 0, s>>>(C, cnorm, k, d, pl.k_pad, pl.n_sub, pl.ntile / 2,
+                                                         (float*)ws->d_b, (float*)ws->d_cn);
         count_launch();
     }
     cudaMemsetAsync(ws->d_count, 0, sizeof(unsigned int), s);
@@ -760,6 +819,8 @@ int gemm_pass(GemmWorkspace* ws, const float* X, int64_t n, int d, int k, const 
     p.NB = pl.NB;
     p.resident = pl.resident;
     p.b_slot_bytes = pl.b_slot_bytes;
+    p.bt = (const float*)ws->d_b;
+    p.cnt = (const float*)ws->d_cn;
     p.xnorm = xnorm;
     p.xlo = xlo;
     p.labels = labels;
@@ -781,15 +842,38 @@ int gemm_pass(GemmWorkspace* ws, const float* X, int64_t n, int d, int k, const 
     p.off_ac = pl.off_ac;
     p.off_scr = pl.off_scr;
     p.off_bar = pl.off_bar;
+    p.trace = nullptr;
+#ifdef B200KM_ENABLE_TRACE
+    const char* trace_path = getenv("B200KM_TRACE");
+    if (trace_path) {
+        cudaMalloc((void**)&p.trace, 16 * 1024 * sizeof(unsigned long long));
+        cudaMemsetAsync(p.trace, 0, 16 * 1024 * sizeof(unsigned long long), s);
+    }
+#endif
     int64_t clusters = p.num_tiles < kNumSMs / 2 ? p.num_tiles : kNumSMs / 2;
     if (clusters < 1) clusters = 1;
-    kmeans_gemm_kernel<<<(unsigned)(2 * clusters), kGmThreads, pl.total, s>>>(tmX, tmB, tmCn, p);
+    kmeans_gemm_kernel<<<(unsigned)(2 * clusters), kGmThreads, pl.total, s>>>(tmX, p);
     count_launch();
     cudaError_t err = cudaGetLastError();
     if (err != cudaSuccess) {
         snprintf(g_gm_err, sizeof(g_gm_err), "tile-GEMM kernel launch failed: %s", cudaGetErrorString(err));
         return 1;
     }
+#ifdef B200KM_ENABLE_TRACE
+    if (p.trace) {  // development aid: synchronous dump of cluster 0's event clocks, one line per index
+        static unsigned long long host[16 * 1024];
+        cudaStreamSynchronize(s);
+        cudaMemcpy(host, p.trace, sizeof(host), cudaMemcpyDeviceToHost);
+        cudaFree(p.trace);
+        if (FILE* f = fopen(trace_path, "w")) {
+            for (int i = 0; i < 1024; ++i) {
+                for (int r = 0; r < 16; ++r) fprintf(f, "%llu ", host[r * 1024 + i]);
+                fprintf(f, "\n");
+            }
+            fclose(f);
+        }
+    }
+#endif
     {
         int64_t blocks = (n + 7) / 8;
         if (blocks > kNumSMs * 8) blocks = kNumSMs * 8;
