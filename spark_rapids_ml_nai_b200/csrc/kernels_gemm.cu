@@ -130,11 +130,29 @@ struct RingPos {
         }
     }
 };
-// contiguous global -> shared bulk copy, completion counted on an mbarrier
-__device__ __forceinline__ void bulk_load(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar) {
-    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst),
-                 "l"(src), "r"(bytes), "r"(bar)
-                 : "memory");
+// Inline wait for the single-thread roles (no call, no labels): try_wait blocks for the hardware's own time limit.
+__device__ __forceinline__ void mbar_wait_inl(uint32_t bar, uint32_t parity) {
+    uint32_t ok;
+    do {
+        asm volatile(
+            "{\n\t"
+            ".reg .pred p;\n\t"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+            "selp.u32 %0, 1, 0, p;\n\t"
+            "}"
+            : "=r"(ok)
+            : "r"(bar), "r"(parity)
+            : "memory");
+    } while (!ok);
+}
+// 2-D tensor load into this CTA's shared memory whose completion bytes are counted on a barrier of the PAIR's
+// leader CTA (`bar` is a shared::cluster address): the MMA issuer waits on one barrier for both halves of an
+// operand.  Plain (non-multicast) load of this GPU's own memory.
+__device__ __forceinline__ void tma_load_2d_pair(uint32_t dst, const CUtensorMap* tm, uint32_t bar, int c0, int c1) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];" ::"r"(dst),
+        "l"(tm), "r"(bar), "r"(c0), "r"(c1)
+        : "memory");
 }
 __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&r)[32]) {
     asm volatile(
@@ -382,7 +400,8 @@ __global__ void __launch_bounds__(256) rowdist_kernel(const float* __restrict__ 
 
 // ------------------------------------------------------------------------------------------------
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kGmThreads, 1)
-    kmeans_gemm_kernel(const __grid_constant__ CUtensorMap tmX, const GmParams p) {
+    kmeans_gemm_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ CUtensorMap tmB,
+                       const __grid_constant__ CUtensorMap tmCn, const GmParams p) {
     if (p.honor_done && p.st->done) return;  // both CTAs of a pair read the same flag
 
     extern __shared__ __align__(1024) uint8_t smem_raw[];
@@ -405,8 +424,8 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kGmThreads, 1)
     uint32_t* tmem_slot = (uint32_t*)(smem + p.off_bar + 288);
 
     if (threadIdx.x == 0) {
-        // the leader's full barriers also collect the peer's "my half has landed" arrival
-        const uint32_t full_count = rank == 0 ? 2u : 1u;
+        // full barriers: used in the leader only; both CTAs' loads count their bytes there
+        const uint32_t full_count = 1u;
         for (int s = 0; s < kMaxNA; ++s) {
             mbar_init(a_full0 + 8u * s, full_count);
             mbar_init(a_empty0 + 8u * s, 1);
@@ -453,37 +472,40 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kGmThreads, 1)
 
     if (warp == 0) {
         // ===================================== TMA producer =====================================
+        // Each CTA loads its half of every operand into its own shared memory; the bytes of both halves are
+        // counted on the leader's barrier (the leader arms it with the total), so nobody relays.
         if (lane == 0) {
             RingPos ar, br;
-            const size_t blk = (size_t)N * 16;  // floats of one B block
+            const uint32_t lead_a_full0 = map_to_cta(a_full0, 0), lead_b_full0 = map_to_cta(b_full0, 0);
+            const int b_rows = N >> 4;       // a B block = N/16 rows of 256 floats in the pre-tiled buffer
+            const int cn_rows = halfN >> 5;  // a norm block = N/64 rows of 256 floats
             for (int64_t tile = cluster_id; tile < p.num_tiles; tile += n_clusters) {
                 const int row0 = (int)(tile * kRowsPair + rank * kRowsCta);
                 int nt = nt0;
                 for (int nti = 0; nti < n_nt; ++nti) {
-                    const float* bt_nt = p.bt + (size_t)(nt * 2 + (int)rank) * (size_t)n_sub * blk;
+                    const int blk0 = (nt * 2 + (int)rank) * n_sub;
                     int sc = sc0;
                     for (int sci = 0; sci < n_sub; ++sci) {
                         if ((sc & 1) == 0 && (!resident || nti == 0)) {  // first touch of this A chunk
-                            mbar_wait(a_empty0 + 8u * ar.slot, ar.phase ^ 1u);
-                            mbar_arrive_expect_tx(a_full0 + 8u * ar.slot, (uint32_t)kASlotBytes);
-                            tma_load_2d(smem_base + p.off_a + ar.slot * kASlotBytes, &tmX, a_full0 + 8u * ar.slot,
-                                        (sc >> 1) * 32, row0);
+                            mbar_wait_inl(a_empty0 + 8u * ar.slot, ar.phase ^ 1u);
+                            if (rank == 0) mbar_arrive_expect_tx(a_full0 + 8u * ar.slot, 2u * (uint32_t)kASlotBytes);
+                            tma_load_2d_pair(smem_base + p.off_a + ar.slot * kASlotBytes, &tmX, lead_a_full0 + 8u * ar.slot,
+                                             (sc >> 1) * 32, row0);
                             ar.next((uint32_t)NA);
                         }
-                        mbar_wait(b_empty0 + 8u * br.slot, br.phase ^ 1u);
+                        mbar_wait_inl(b_empty0 + 8u * br.slot, br.phase ^ 1u);
                         gtrace(p, 0, (uint32_t)sci);
-                        mbar_arrive_expect_tx(b_full0 + 8u * br.slot, (uint32_t)p.b_slot_bytes);
-                        bulk_load(smem_base + p.off_b + br.slot * p.b_slot_bytes, bt_nt + (size_t)sc * blk,
-                                  (uint32_t)p.b_slot_bytes, b_full0 + 8u * br.slot);
+                        if (rank == 0) mbar_arrive_expect_tx(b_full0 + 8u * br.slot, 2u * (uint32_t)p.b_slot_bytes);
+                        tma_load_2d_pair(smem_base + p.off_b + br.slot * p.b_slot_bytes, &tmB, lead_b_full0 + 8u * br.slot, 0,
+                                         (blk0 + sc) * b_rows);
                         br.next((uint32_t)NB);
                         if (++sc == n_sub) sc = 0;
                     }
                     {  // the norm K-step of this N-tile
-                        mbar_wait(b_empty0 + 8u * br.slot, br.phase ^ 1u);
-                        mbar_arrive_expect_tx(b_full0 + 8u * br.slot, (uint32_t)(halfN * 32));
-                        bulk_load(smem_base + p.off_b + br.slot * p.b_slot_bytes,
-                                  p.cnt + (size_t)(nt * 2 + (int)rank) * (size_t)(halfN * 8), (uint32_t)(halfN * 32),
-                                  b_full0 + 8u * br.slot);
+                        mbar_wait_inl(b_empty0 + 8u * br.slot, br.phase ^ 1u);
+                        if (rank == 0) mbar_arrive_expect_tx(b_full0 + 8u * br.slot, 2u * (uint32_t)(halfN * 32));
+                        tma_load_2d_pair(smem_base + p.off_b + br.slot * p.b_slot_bytes, &tmCn, lead_b_full0 + 8u * br.slot, 0,
+                                         (nt * 2 + (int)rank) * cn_rows);
                         br.next((uint32_t)NB);
                     }
                     if (++nt == n_nt) nt = 0;
@@ -491,10 +513,9 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kGmThreads, 1)
             }
         }
         __syncwarp();
-    } else if (warp == 1) {
-        // ================================ MMA issuer (leader) / relay (peer) ================================
-        // Leader: the whole warp runs the loop, one elected lane issues.  Peer: the same walk over the rings; as
-        // each of its slots lands it arrives on the leader's barrier of that slot.
+    } else if (warp == 1 && rank == 0) {
+        // ====================================== MMA issuer (leader CTA) ======================================
+        // The whole warp runs the loop, one elected lane issues.
         const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(kRowsPair >> 4) << 24) |
                                ((uint32_t)(N >> 3) << 17);
         const uint64_t adesc0 = make_b_desc(smem_base + p.off_a, 128);
@@ -503,25 +524,20 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kGmThreads, 1)
         const uint64_t acdesc = make_b_desc(smem_base + p.off_ac, 32);
         const uint64_t lo_off = (uint64_t)((halfN * 64) >> 4);
         const uint32_t b_slot16 = (uint32_t)p.b_slot_bytes >> 4;
-        const uint32_t lead_a_full0 = map_to_cta(a_full0, 0), lead_b_full0 = map_to_cta(b_full0, 0);
         RingPos ar, br;
         uint32_t gnt = 0;
         for (int64_t tile = cluster_id; tile < p.num_tiles; tile += n_clusters) {
             for (int nti = 0; nti < n_nt; ++nti, ++gnt) {
                 const uint32_t buf = gnt & 1u;
                 const uint32_t d_tmem = tmem_base + buf * 256u;
-                if (rank == 0) {
-                    mbar_wait(d_empty0 + 8u * buf, ((gnt >> 1) & 1u) ^ 1u);
-                    tc_fence_after();
-                }
+                mbar_wait_inl(d_empty0 + 8u * buf, ((gnt >> 1) & 1u) ^ 1u);
                 uint32_t aslot = 0, a_idx = 0;
                 int sc = sc0;
                 for (int sci = 0; sci < n_sub; ++sci) {
                     if ((sc & 1) == 0) {
                         if (!resident || nti == 0) {
                             aslot = ar.slot;
-                            mbar_wait(a_full0 + 8u * aslot, ar.phase);
-                            if (rank != 0 && lane == 0) mbar_arrive_cluster(lead_a_full0 + 8u * aslot);
+                            mbar_wait_inl(a_full0 + 8u * aslot, ar.phase);
                             ar.next((uint32_t)NA);
                         } else {
                             aslot = a_idx;  // resident: the chunks sit in the slots in this cluster's load order
@@ -529,43 +545,37 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kGmThreads, 1)
                         ++a_idx;
                     }
                     const uint32_t bslot = br.slot;
-                    mbar_wait(b_full0 + 8u * bslot, br.phase);
-                    if (rank != 0 && lane == 0) mbar_arrive_cluster(lead_b_full0 + 8u * bslot);
+                    mbar_wait_inl(b_full0 + 8u * bslot, br.phase);
                     br.next((uint32_t)NB);
-                    if (rank == 0) {
-                        tc_fence_after();
-                        if (lane == 0) gtrace(p, 1, (uint32_t)sci);
-                        if (elect_one()) {
-                            // A: 64-byte half (sc & 1) of the 128-byte row, K-steps of 32 bytes
-                            const uint64_t ad = adesc0 + (uint64_t)((aslot << 10) + (uint32_t)((sc & 1) * 4));
-                            const uint64_t bd = bdesc0 + (uint64_t)(bslot * b_slot16);
+                    tc_fence_after();
+                    if (lane == 0) gtrace(p, 1, (uint32_t)sci);
+                    if (elect_one()) {
+                        // A: 64-byte half (sc & 1) of the 128-byte row, K-steps of 32 bytes
+                        const uint64_t ad = adesc0 + (uint64_t)((aslot << 10) + (uint32_t)((sc & 1) * 4));
+                        const uint64_t bd = bdesc0 + (uint64_t)(bslot * b_slot16);
 #pragma unroll
-                            for (int kk = 0; kk < 2; ++kk) {
-                                mma_tf32_ss2(d_tmem, ad + 2 * kk, bd + 2 * kk, idesc, (sci | kk) != 0);
-                                mma_tf32_ss2(d_tmem, ad + 2 * kk, bd + lo_off + 2 * kk, idesc, 1);
-                            }
-                            tc_commit_pair(b_empty0 + 8u * bslot);
-                            const bool a_done = ((sc & 1) == 1 || sc == n_sub - 1) && (!resident || nti == n_nt - 1);
-                            if (a_done) tc_commit_pair(a_empty0 + 8u * aslot);
+                        for (int kk = 0; kk < 2; ++kk) {
+                            mma_tf32_ss2(d_tmem, ad + 2 * kk, bd + 2 * kk, idesc, (sci | kk) != 0);
+                            mma_tf32_ss2(d_tmem, ad + 2 * kk, bd + lo_off + 2 * kk, idesc, 1);
                         }
-                        __syncwarp();
+                        tc_commit_pair(b_empty0 + 8u * bslot);
+                        const bool a_done = ((sc & 1) == 1 || sc == n_sub - 1) && (!resident || nti == n_nt - 1);
+                        if (a_done) tc_commit_pair(a_empty0 + 8u * aslot);
                     }
+                    __syncwarp();
                     if (++sc == n_sub) sc = 0;
                 }
                 {  // the norm K-step closes the N-tile
                     const uint32_t bslot = br.slot;
-                    mbar_wait(b_full0 + 8u * bslot, br.phase);
-                    if (rank != 0 && lane == 0) mbar_arrive_cluster(lead_b_full0 + 8u * bslot);
+                    mbar_wait_inl(b_full0 + 8u * bslot, br.phase);
                     br.next((uint32_t)NB);
-                    if (rank == 0) {
-                        tc_fence_after();
-                        if (elect_one()) {
-                            mma_tf32_ss2(d_tmem, acdesc, cdesc0 + (uint64_t)(bslot * b_slot16), idesc, 1);
-                            tc_commit_pair(b_empty0 + 8u * bslot);
-                            tc_commit_pair(d_full0 + 8u * buf);
-                        }
-                        __syncwarp();
+                    tc_fence_after();
+                    if (elect_one()) {
+                        mma_tf32_ss2(d_tmem, acdesc, cdesc0 + (uint64_t)(bslot * b_slot16), idesc, 1);
+                        tc_commit_pair(b_empty0 + 8u * bslot);
+                        tc_commit_pair(d_full0 + 8u * buf);
                     }
+                    __syncwarp();
                 }
             }
         }
@@ -716,6 +726,28 @@ Plan make_plan(int d, int k) {
     return pl;
 }
 
+// Tensor map over a flat float buffer seen as [rows][256], box = box_rows full rows, no swizzle: the box lands in
+// shared memory as box_rows * 1024 contiguous bytes.
+int encode_flat(char* err, size_t err_len, CUtensorMap* tm, const void* base, uint64_t rows, uint32_t box_rows) {
+    EncodeTiledFn enc = get_encode();
+    if (!enc) {
+        snprintf(err, err_len, "cuTensorMapEncodeTiled not available from the driver");
+        return 1;
+    }
+    cuuint64_t dims[2] = {256, rows};
+    cuuint64_t strides[1] = {1024};
+    cuuint32_t box[2] = {256, box_rows};
+    cuuint32_t estr[2] = {1, 1};
+    CUresult r = enc(tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<void*>(base), dims, strides, box, estr,
+                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) {
+        snprintf(err, err_len, "cuTensorMapEncodeTiled (flat) failed with CUresult %d", (int)r);
+        return 1;
+    }
+    return 0;
+}
+
 template <typename T>
 int grow_buf(T** p, size_t* cap, size_t need, const char* what) {
     if (need <= *cap && *p) return 0;
@@ -784,8 +816,14 @@ int gemm_pass(GemmWorkspace* ws, const float* X, int64_t n, int d, int k, const 
         snprintf(g_gm_err, sizeof(g_gm_err), "cudaMalloc of the open-row counter failed");
         return 1;
     }
-    CUtensorMap tmX;
-    if (encode_2d(g_gm_err, sizeof(g_gm_err), &tmX, X, (uint64_t)d, (uint64_t)n, (uint64_t)d * 4, 32, kRowsCta)) return 1;
+    // X: 128-row x 32-float boxes (SWIZZLE_128B).  The pre-tiled operands are read as rows of 256 floats without
+    // swizzle, so that a ring slot (a contiguous block of the buffer) is one box.
+    CUtensorMap tmX, tmB, tmCn;
+    char* e = g_gm_err;
+    const size_t el = sizeof(g_gm_err);
+    if (encode_2d(e, el, &tmX, X, (uint64_t)d, (uint64_t)n, (uint64_t)d * 4, 32, kRowsCta)) return 1;
+    if (encode_flat(e, el, &tmB, ws->d_b, 2 * (uint64_t)pl.k_pad * pl.d_pad / 256, (uint32_t)(pl.ntile / 16))) return 1;
+    if (encode_flat(e, el, &tmCn, ws->d_cn, 8 * (uint64_t)pl.k_pad / 256, (uint32_t)(pl.ntile / 64))) return 1;
 
     static PerDeviceOnce attr_set;  // the opt-in is a per-device attribute
     const int dev = PerDeviceOnce::current();
@@ -852,7 +890,7 @@ int gemm_pass(GemmWorkspace* ws, const float* X, int64_t n, int d, int k, const 
 #endif
     int64_t clusters = p.num_tiles < kNumSMs / 2 ? p.num_tiles : kNumSMs / 2;
     if (clusters < 1) clusters = 1;
-    kmeans_gemm_kernel<<<(unsigned)(2 * clusters), kGmThreads, pl.total, s>>>(tmX, p);
+    kmeans_gemm_kernel<<<(unsigned)(2 * clusters), kGmThreads, pl.total, s>>>(tmX, tmB, tmCn, p);
     count_launch();
     cudaError_t err = cudaGetLastError();
     if (err != cudaSuccess) {
