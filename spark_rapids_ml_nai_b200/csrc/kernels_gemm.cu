@@ -52,6 +52,7 @@ constexpr int kConstABytes = kRowsCta * 32;  // the -0.5 tile: 128 rows x 8 floa
 constexpr int kScrBytes = 5 * kRowsCta * 4;  // hand-over of the column halves: (b1, cb1, b2, cb2, b3) per row
 constexpr int kBarBytes = 512;
 constexpr int kMaxSmem = 227 * 1024;
+constexpr int kCntOpen = 0, kCntScan = 1, kCntCand = 2, kCntOverflow = 3;
 constexpr float kCnPad = 1e30f;  // "norm" of the padded centroid columns: their score is -5e29
 
 struct GmParams {
@@ -68,8 +69,12 @@ struct GmParams {
     const float* xnorm;
     const float* xlo;
     int32_t* labels;
-    uint2* open;  // (row, runner-up | mode << 24) of every row the TF32 scores did not decide
-    unsigned int* open_count;
+    uint4* open;  // (row, runner-up | mode << 24, score threshold, -) of every row the TF32 scores did not decide
+    unsigned int* counters;  // [kCntOpen, kCntScan, kCntCand, kCntOverflow]
+    // second pass over the gathered multi-candidate rows (EMIT instantiation): n comes from counters[kCntScan]
+    const float* thr;      // per gathered row: every centroid scoring above it is a candidate
+    uint2* cand;           // (gathered row, centroid)
+    unsigned int cand_cap, scan_cap;
     IterState* st;
     int honor_done;
     float tol_x, eps_rel, abs_rel;
@@ -319,68 +324,119 @@ __device__ __forceinline__ double sqdist_f64(const float* __restrict__ x, const 
     return s;
 }
 
-// One warp per listed row.  mode 0: exactly the computed best (labels[row]) against the runner-up; mode 1: every
-// centroid.  FP32 squared differences (no cancellation), float64 among those that tie; ties keep the lowest index.
+// One warp per listed row.  mode 0: exactly the computed best (labels[row]) against the runner-up, FP32 squared
+// differences (no cancellation), float64 when those tie; ties keep the lowest index.  mode 1 (more candidates):
+// the row is copied into the gather buffer for the second GEMM pass, which lists its candidates.
 __global__ void __launch_bounds__(256) gemm_fixup_kernel(const float* __restrict__ X, int d, int k,
-                                                         const float* __restrict__ C, const uint2* __restrict__ open,
-                                                         const unsigned int* __restrict__ open_count,
-                                                         int32_t* __restrict__ labels, IterState* st, int honor_done) {
+                                                         const float* __restrict__ C, const uint4* __restrict__ open,
+                                                         unsigned int* __restrict__ counters, int32_t* __restrict__ labels,
+                                                         float* __restrict__ xs, unsigned int* __restrict__ scan_row,
+                                                         float* __restrict__ scan_thr, unsigned long long* __restrict__ scan_key,
+                                                         unsigned int scan_cap, IterState* st, int honor_done) {
     if (honor_done && st->done) return;
-    const unsigned int count = *open_count;
+    const unsigned int count = counters[kCntOpen];
     const int lane = threadIdx.x & 31;
     const unsigned int warp0 = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     const unsigned int nwarps = gridDim.x * (blockDim.x >> 5);
     const int nchunks = d >> 2;
     for (unsigned int w = warp0; w < count; w += nwarps) {
-        const uint2 e = open[w];
+        const uint4 e = open[w];
         const int64_t row = e.x;
         const int i2 = (int)(e.y & 0xFFFFFFu);
         const int mode = (int)(e.y >> 24);
-        const int i1 = labels[row];
         const float* x = X + (size_t)row * d;
         const float4* x4 = reinterpret_cast<const float4*>(x);
-        int bi;
         if (mode == 0) {
+            const int i1 = labels[row];
             const int ja = min(i1, i2), jb = max(i1, i2);
             const float sa = sqdist_f32(x4, reinterpret_cast<const float4*>(C + (size_t)ja * d), nchunks, lane);
             const float sb = sqdist_f32(x4, reinterpret_cast<const float4*>(C + (size_t)jb * d), nchunks, lane);
-            bi = sb < sa ? jb : ja;
+            int bi = sb < sa ? jb : ja;
             if (fabsf(sa - sb) <= 4e-6f * (sa + sb)) {
                 const double da = sqdist_f64(x, C + (size_t)ja * d, d, lane);
                 const double db = sqdist_f64(x, C + (size_t)jb * d, d, lane);
                 bi = db < da ? jb : ja;
             }
+            if (bi != i1 && lane == 0) labels[row] = bi;
         } else {
-            float f1 = FLT_MAX, f2 = FLT_MAX;
-            bi = 0;
-            for (int j = 0; j < k; ++j) {
-                const float sum = sqdist_f32(x4, reinterpret_cast<const float4*>(C + (size_t)j * d), nchunks, lane);
-                if (sum < f1) {  // ascending index order: ties keep the lowest
-                    f2 = f1;
-                    f1 = sum;
-                    bi = j;
-                } else {
-                    f2 = fminf(f2, sum);
-                }
+            unsigned int pos = 0;
+            if (lane == 0) pos = atomicAdd(counters + kCntScan, 1u);
+            pos = __shfl_sync(0xffffffffu, pos, 0);
+            if (pos >= scan_cap) {
+                if (lane == 0) counters[kCntOverflow] = 1u;
+                continue;
             }
-            if (f2 < FLT_MAX && (f2 - f1) <= 4e-6f * (f1 + f2)) {
-                // float64 among the centroids inside the FP32 band of the best
-                const float lim = f1 + 8e-6f * (f1 + f2);
-                double bd = DBL_MAX;
-                for (int j = 0; j < k; ++j) {
-                    const float sum = sqdist_f32(x4, reinterpret_cast<const float4*>(C + (size_t)j * d), nchunks, lane);
-                    if (sum > lim) continue;
-                    const double s64 = sqdist_f64(x, C + (size_t)j * d, d, lane);
-                    if (s64 < bd) {
-                        bd = s64;
-                        bi = j;
-                    }
-                }
+            float4* dst = reinterpret_cast<float4*>(xs + (size_t)pos * d);
+            for (int ch = lane; ch < nchunks; ch += 32) dst[ch] = __ldg(x4 + ch);
+            if (lane == 0) {
+                scan_row[pos] = (unsigned int)row;
+                scan_thr[pos] = __uint_as_float(e.z);
+                scan_key[pos] = ~0ull;
             }
         }
-        if (bi != i1 && lane == 0) labels[row] = bi;
     }
     if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(&st->screen_refined, count);
+}
+
+// One warp per candidate (gathered row, centroid): FP32 squared differences; the row keeps the smallest
+// (distance, index) through a 64-bit atomic minimum (equal distances: the lowest index).
+__global__ void __launch_bounds__(256) gemm_cand_kernel(const float* __restrict__ xs, int d, const float* __restrict__ C,
+                                                        const uint2* __restrict__ cand,
+                                                        const unsigned int* __restrict__ counters, unsigned int cand_cap,
+                                                        unsigned long long* __restrict__ scan_key, IterState* st,
+                                                        int honor_done) {
+    if (honor_done && st->done) return;
+    if (counters[kCntOverflow]) return;
+    unsigned int count = counters[kCntCand];
+    if (count > cand_cap) count = cand_cap;
+    const int lane = threadIdx.x & 31;
+    const unsigned int warp0 = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    const unsigned int nwarps = gridDim.x * (blockDim.x >> 5);
+    const int nchunks = d >> 2;
+    for (unsigned int w = warp0; w < count; w += nwarps) {
+        const uint2 e = cand[w];
+        const float v = sqdist_f32(reinterpret_cast<const float4*>(xs + (size_t)e.x * d),
+                                   reinterpret_cast<const float4*>(C + (size_t)e.y * d), nchunks, lane);
+        if (lane == 0) atomicMin(scan_key + e.x, ((unsigned long long)__float_as_uint(v) << 32) | (unsigned long long)e.y);
+    }
+}
+
+// Labels of the gathered rows from their (distance, index) minima - or, when the gather / candidate buffers
+// overflowed (degenerate data: very many equidistant centroids), every centroid for every such row.
+__global__ void __launch_bounds__(256) gemm_scan_finish_kernel(const float* __restrict__ X, int d, int k,
+                                                               const float* __restrict__ C, const uint4* __restrict__ open,
+                                                               const unsigned int* __restrict__ counters,
+                                                               const unsigned int* __restrict__ scan_row,
+                                                               const unsigned long long* __restrict__ scan_key,
+                                                               int32_t* __restrict__ labels, IterState* st, int honor_done) {
+    if (honor_done && st->done) return;
+    if (!counters[kCntOverflow]) {
+        const unsigned int m = counters[kCntScan];
+        for (unsigned int i = blockIdx.x * blockDim.x + threadIdx.x; i < m; i += gridDim.x * blockDim.x)
+            labels[scan_row[i]] = (int32_t)(scan_key[i] & 0xFFFFFFFFull);
+        return;
+    }
+    const unsigned int count = counters[kCntOpen];
+    const int lane = threadIdx.x & 31;
+    const unsigned int warp0 = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    const unsigned int nwarps = gridDim.x * (blockDim.x >> 5);
+    const int nchunks = d >> 2;
+    for (unsigned int w = warp0; w < count; w += nwarps) {
+        const uint4 e = open[w];
+        if ((e.y >> 24) == 0) continue;
+        const int64_t row = e.x;
+        const float4* x4 = reinterpret_cast<const float4*>(X + (size_t)row * d);
+        float f1 = FLT_MAX;
+        int bi = 0;
+        for (int j = 0; j < k; ++j) {
+            const float sum = sqdist_f32(x4, reinterpret_cast<const float4*>(C + (size_t)j * d), nchunks, lane);
+            if (sum < f1) {  // ascending index order: ties keep the lowest
+                f1 = sum;
+                bi = j;
+            }
+        }
+        if (lane == 0) labels[row] = bi;
+    }
 }
 
 // best[i] = ||x_i - c_label(i)||^2 from FP32 differences: one warp per row.
@@ -399,10 +455,21 @@ __global__ void __launch_bounds__(256) rowdist_kernel(const float* __restrict__ 
 }
 
 // ------------------------------------------------------------------------------------------------
+// EMIT = false: the assignment pass (labels + open-row list).  EMIT = true: the same GEMM over the gathered rows
+// that have more than two candidates; instead of ranking, the epilogue lists every centroid whose score reaches
+// the row's threshold (the exact distances of those few are then compared by gemm_cand_kernel).
+template <bool EMIT>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kGmThreads, 1)
     kmeans_gemm_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ CUtensorMap tmB,
-                       const __grid_constant__ CUtensorMap tmCn, const GmParams p) {
+                       const __grid_constant__ CUtensorMap tmCn, GmParams p) {
     if (p.honor_done && p.st->done) return;  // both CTAs of a pair read the same flag
+    if (EMIT) {
+        if (p.counters[kCntOverflow]) return;  // too many such rows for the gather buffer: the brute-force kernel runs
+        unsigned int m = p.counters[kCntScan];
+        p.n = m;
+        p.num_tiles = (m + kRowsPair - 1) / kRowsPair;
+        if (p.num_tiles == 0) return;
+    }
 
     extern __shared__ __align__(1024) uint8_t smem_raw[];
     uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
@@ -585,17 +652,18 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kGmThreads, 1)
         const int half = (warp - kEpiWarp0) >> 2;
         const int row = q * 32 + lane;
         float* scr = (float*)(smem + p.off_scr);
-        const float cmax = p.st->cnorm_max;
+        const float cmax = EMIT ? 0.f : p.st->cnorm_max;
         const uint32_t my_d_empty0 = map_to_cta(d_empty0, 0);
         uint32_t gnt = 0;
         for (int64_t tile = cluster_id; tile < p.num_tiles; tile += n_clusters) {
             const int64_t grow = tile * kRowsPair + rank * kRowsCta + row;
             const bool valid = grow < p.n;
             float xn = 0.f, xl = 0.f;
-            if (valid && half == 0) {  // consumed after the last N-tile
+            if (!EMIT && valid && half == 0) {  // consumed after the last N-tile
                 xn = p.xnorm[grow];
                 xl = p.xlo[grow];
             }
+            const float thr = (EMIT && valid) ? p.thr[grow] : FLT_MAX;
             float b1 = -FLT_MAX, b2 = -FLT_MAX, b3 = -FLT_MAX;
             int cb1 = 0, cb2 = 0;
             int nt = nt0;
@@ -616,17 +684,31 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kGmThreads, 1)
                         __syncwarp();
                         if (lane == 0) mbar_arrive_cluster(my_d_empty0 + 8u * buf);
                     }
-                    float key[32];
-#pragma unroll
-                    for (int j = 0; j < 32; ++j) key[j] = __uint_as_float((sc[j] & ~31u) | (uint32_t)j);
-                    float t1, t2, t3;
-                    top3max_of_32(key, t1, t2, t3);
                     const int col0 = nt * N + half * halfN + c0;
-                    merge3(b1, cb1, b2, cb2, b3, t1, col0, t2, col0, t3);
+                    if constexpr (EMIT) {
+                        unsigned hit = 0;
+#pragma unroll
+                        for (int j = 0; j < 32; ++j) hit |= (__uint_as_float(sc[j]) >= thr ? 1u : 0u) << j;
+                        while (hit) {
+                            const int j = __ffs(hit) - 1;
+                            hit &= hit - 1;
+                            const unsigned int pos = atomicAdd(p.counters + kCntCand, 1u);
+                            if (pos < p.cand_cap) p.cand[pos] = make_uint2((unsigned int)grow, (unsigned int)(col0 + j));
+                            else p.counters[kCntOverflow] = 1u;
+                        }
+                    } else {
+                        float key[32];
+#pragma unroll
+                        for (int j = 0; j < 32; ++j) key[j] = __uint_as_float((sc[j] & ~31u) | (uint32_t)j);
+                        float t1, t2, t3;
+                        top3max_of_32(key, t1, t2, t3);
+                        merge3(b1, cb1, b2, cb2, b3, t1, col0, t2, col0, t3);
+                    }
                 }
                 if (warp == kEpiWarp0 && lane == 0) gtrace(p, 4, gnt * 2 + 1);
                 if (++nt == n_nt) nt = 0;
             }
+            if (EMIT) continue;
             // ---- the two column halves of a row meet; half 0 decides ----
             if (half == 1) {
                 scr[0 * kRowsCta + row] = b1;
@@ -652,16 +734,23 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kGmThreads, 1)
                 const float r3 = sqrtf(fmaxf(D3, 0.f) + pad);
                 const bool open = valid && p.k > 1 && (D2 - D1) < 2.f * t * (r1 + r2) + eps;
                 const bool third = open && p.k > 2 && (D3 - D1) < 2.f * t * (r1 + r3) + eps;
+                // More than two candidates: every centroid j that can still be the nearest has D_j - D_1 below
+                // 2 t (r_1 + r_j) + eps; with B = 4 t r_1 + eps that implies D_j < D_1 + 2 B (t << r_1), hence
+                // r_j <= sqrt(D_1 + 2 B + pad) and, in score units, score_j > score_1 - band / 2.
+                const float B = 4.f * t * r1 + eps;
+                const float band = 2.f * t * (r1 + sqrtf(fmaxf(D1, 0.f) + 2.f * B + pad)) + 2.f * eps;
+                const float thr_row = b1 - 0.5f * band;
                 if (valid) p.labels[grow] = i1;
                 const unsigned m = __ballot_sync(0xffffffffu, open);
                 if (m) {
                     const int leader = __ffs(m) - 1;
                     unsigned int base = 0;
-                    if (lane == leader) base = atomicAdd(p.open_count, (unsigned int)__popc(m));
+                    if (lane == leader) base = atomicAdd(p.counters + kCntOpen, (unsigned int)__popc(m));
                     base = __shfl_sync(0xffffffffu, base, leader);
                     if (open)
                         p.open[base + __popc(m & ((1u << lane) - 1u))] =
-                            make_uint2((unsigned int)grow, (unsigned int)i2 | (third ? (1u << 24) : 0u));
+                            make_uint4((unsigned int)grow, (unsigned int)i2 | (third ? (1u << 24) : 0u),
+                                       __float_as_uint(thr_row), 0u);
                 }
             }
             named_bar_sync(2, 256);
@@ -772,7 +861,11 @@ bool gemm_supported(const float* X, int d, int k) {
 size_t gemm_workspace_bytes(int64_t n, int d, int k) {
     const Plan pl = make_plan(d, k);
     if (!pl.ok) return 0;
-    return sizeof(float) * (2 * (size_t)pl.k_pad * pl.d_pad + 8 * (size_t)pl.k_pad) + 8 * ((size_t)n + (size_t)n / 8 + 64) + 64;
+    size_t scan = (size_t)n / 4 < 4096 ? 4096 : (size_t)n / 4;
+    if (scan * (size_t)d * 4 > ((size_t)2 << 30)) scan = ((size_t)2 << 30) / ((size_t)d * 4);
+    scan += scan / 8 + kRowsPair;
+    return sizeof(float) * (2 * (size_t)pl.k_pad * pl.d_pad + 8 * (size_t)pl.k_pad) + 16 * ((size_t)n + (size_t)n / 8 + 64) + 64 +
+           scan * ((size_t)d * 4 + 16 + 8 * 8);
 }
 const char* gemm_last_error() { return g_gm_err; }
 
@@ -781,6 +874,8 @@ void gemm_free(GemmWorkspace* ws) {
     if (ws->d_cn) cudaFree(ws->d_cn);
     if (ws->d_open) cudaFree(ws->d_open);
     if (ws->d_count) cudaFree(ws->d_count);
+    for (void* q : {ws->d_xs, ws->d_scan_row, ws->d_scan_thr, ws->d_scan_key, ws->d_cand})
+        if (q) cudaFree(q);
     *ws = GemmWorkspace();
 }
 
@@ -811,24 +906,48 @@ int gemm_pass(GemmWorkspace* ws, const float* X, int64_t n, int d, int k, const 
     if (n <= 0) return 0;
     if (grow_buf((float**)&ws->d_b, &ws->b_cap, 2 * (size_t)pl.k_pad * pl.d_pad, "the TF32 centroids")) return 1;
     if (grow_buf((float**)&ws->d_cn, &ws->cn_cap, 8 * (size_t)pl.k_pad, "the centroid norms")) return 1;
-    if (grow_buf((uint2**)&ws->d_open, &ws->open_cap, (size_t)n, "the open-row list")) return 1;
+    if (grow_buf((uint4**)&ws->d_open, &ws->open_cap, (size_t)n, "the open-row list")) return 1;
     if (!ws->d_count && cudaMalloc((void**)&ws->d_count, 64) != cudaSuccess) {
         snprintf(g_gm_err, sizeof(g_gm_err), "cudaMalloc of the open-row counter failed");
         return 1;
     }
+    // second pass: gather buffer for the rows with more than two candidates (n / 4 rows, at most 2 GB) and the
+    // candidate list; beyond that capacity the brute-force kernel takes over
+    size_t scan_cap = (size_t)n / 4 < 4096 ? 4096 : (size_t)n / 4;
+    if (scan_cap * (size_t)d * 4 > ((size_t)2 << 30)) scan_cap = ((size_t)2 << 30) / ((size_t)d * 4);
+    scan_cap = (scan_cap + kRowsPair - 1) / kRowsPair * kRowsPair;
+    const size_t cand_cap = 8 * scan_cap;
+    if (ws->scan_cap < scan_cap || ws->scan_d < (size_t)d) {
+        const size_t rows = scan_cap + scan_cap / 8;
+        for (void** q : {&ws->d_xs, &ws->d_scan_row, &ws->d_scan_thr, &ws->d_scan_key, &ws->d_cand}) {
+            if (*q) cudaFree(*q);
+            *q = nullptr;
+        }
+        ws->scan_cap = 0;
+        if (cudaMalloc(&ws->d_xs, rows * (size_t)d * 4) != cudaSuccess || cudaMalloc(&ws->d_scan_row, rows * 4) != cudaSuccess ||
+            cudaMalloc(&ws->d_scan_thr, rows * 4) != cudaSuccess || cudaMalloc(&ws->d_scan_key, rows * 8) != cudaSuccess ||
+            cudaMalloc(&ws->d_cand, 8 * rows * 8) != cudaSuccess) {
+            snprintf(g_gm_err, sizeof(g_gm_err), "cudaMalloc of the second-pass buffers (%zu rows x %d) failed", rows, d);
+            return 1;
+        }
+        ws->scan_cap = rows;
+        ws->scan_d = (size_t)d;
+    }
     // X: 128-row x 32-float boxes (SWIZZLE_128B).  The pre-tiled operands are read as rows of 256 floats without
     // swizzle, so that a ring slot (a contiguous block of the buffer) is one box.
-    CUtensorMap tmX, tmB, tmCn;
+    CUtensorMap tmX, tmXs, tmB, tmCn;
     char* e = g_gm_err;
     const size_t el = sizeof(g_gm_err);
     if (encode_2d(e, el, &tmX, X, (uint64_t)d, (uint64_t)n, (uint64_t)d * 4, 32, kRowsCta)) return 1;
+    if (encode_2d(e, el, &tmXs, ws->d_xs, (uint64_t)d, (uint64_t)scan_cap, (uint64_t)d * 4, 32, kRowsCta)) return 1;
     if (encode_flat(e, el, &tmB, ws->d_b, 2 * (uint64_t)pl.k_pad * pl.d_pad / 256, (uint32_t)(pl.ntile / 16))) return 1;
     if (encode_flat(e, el, &tmCn, ws->d_cn, 8 * (uint64_t)pl.k_pad / 256, (uint32_t)(pl.ntile / 64))) return 1;
 
     static PerDeviceOnce attr_set;  // the opt-in is a per-device attribute
     const int dev = PerDeviceOnce::current();
     if (dev < 0 || !attr_set.done[dev]) {
-        if (cudaFuncSetAttribute(kmeans_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxSmem) != cudaSuccess) {
+        if (cudaFuncSetAttribute(kmeans_gemm_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxSmem) != cudaSuccess ||
+            cudaFuncSetAttribute(kmeans_gemm_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxSmem) != cudaSuccess) {
             snprintf(g_gm_err, sizeof(g_gm_err), "cannot raise dynamic shared memory to %d bytes", kMaxSmem);
             return 1;
         }
@@ -842,7 +961,7 @@ int gemm_pass(GemmWorkspace* ws, const float* X, int64_t n, int d, int k, const 
                                                          (float*)ws->d_b, (float*)ws->d_cn);
         count_launch();
     }
-    cudaMemsetAsync(ws->d_count, 0, sizeof(unsigned int), s);
+    cudaMemsetAsync(ws->d_count, 0, 64, s);
 
     GmParams p;
     p.n = n;
@@ -862,8 +981,12 @@ int gemm_pass(GemmWorkspace* ws, const float* X, int64_t n, int d, int k, const 
     p.xnorm = xnorm;
     p.xlo = xlo;
     p.labels = labels;
-    p.open = (uint2*)ws->d_open;
-    p.open_count = (unsigned int*)ws->d_count;
+    p.open = (uint4*)ws->d_open;
+    p.counters = (unsigned int*)ws->d_count;
+    p.thr = (const float*)ws->d_scan_thr;
+    p.cand = (uint2*)ws->d_cand;
+    p.cand_cap = (unsigned int)cand_cap;
+    p.scan_cap = (unsigned int)scan_cap;
     p.st = st;
     p.honor_done = honor_done ? 1 : 0;
     // Error model (file header; the same as kernels_screen.cu).  x is read truncated to TF32, ||x - x^|| is the
@@ -890,7 +1013,7 @@ int gemm_pass(GemmWorkspace* ws, const float* X, int64_t n, int d, int k, const 
 #endif
     int64_t clusters = p.num_tiles < kNumSMs / 2 ? p.num_tiles : kNumSMs / 2;
     if (clusters < 1) clusters = 1;
-    kmeans_gemm_kernel<<<(unsigned)(2 * clusters), kGmThreads, pl.total, s>>>(tmX, tmB, tmCn, p);
+    kmeans_gemm_kernel<false><<<(unsigned)(2 * clusters), kGmThreads, pl.total, s>>>(tmX, tmB, tmCn, p);
     count_launch();
     cudaError_t err = cudaGetLastError();
     if (err != cudaSuccess) {
@@ -913,11 +1036,35 @@ int gemm_pass(GemmWorkspace* ws, const float* X, int64_t n, int d, int k, const 
     }
 #endif
     {
+        // exact decisions: pairs at once; rows with more candidates are gathered, scored again by the same GEMM
+        // with the listing epilogue, and decided among the listed centroids
+        const int hd = honor_done ? 1 : 0;
         int64_t blocks = (n + 7) / 8;
         if (blocks > kNumSMs * 8) blocks = kNumSMs * 8;
-        gemm_fixup_kernel<<<(unsigned)blocks, 256, 0, s>>>(X, d, k, C, (const uint2*)ws->d_open,
-                                                          (const unsigned int*)ws->d_count, labels, st, honor_done ? 1 : 0);
+        unsigned int* counters = (unsigned int*)ws->d_count;
+        gemm_fixup_kernel<<<(unsigned)blocks, 256, 0, s>>>(X, d, k, C, (const uint4*)ws->d_open, counters, labels,
+                                                          (float*)ws->d_xs, (unsigned int*)ws->d_scan_row,
+                                                          (float*)ws->d_scan_thr, (unsigned long long*)ws->d_scan_key,
+                                                          (unsigned int)scan_cap, st, hd);
         count_launch();
+        int64_t clusters2 = (int64_t)(scan_cap / kRowsPair) < kNumSMs / 2 ? (int64_t)(scan_cap / kRowsPair) : kNumSMs / 2;
+        if (clusters2 < 1) clusters2 = 1;
+        GmParams p2 = p;
+        p2.trace = nullptr;
+        kmeans_gemm_kernel<true><<<(unsigned)(2 * clusters2), kGmThreads, pl.total, s>>>(tmXs, tmB, tmCn, p2);
+        count_launch();
+        gemm_cand_kernel<<<kNumSMs * 8, 256, 0, s>>>((const float*)ws->d_xs, d, C, (const uint2*)ws->d_cand, counters,
+                                                    (unsigned int)cand_cap, (unsigned long long*)ws->d_scan_key, st, hd);
+        count_launch();
+        gemm_scan_finish_kernel<<<kNumSMs * 8, 256, 0, s>>>(X, d, k, C, (const uint4*)ws->d_open, counters,
+                                                           (const unsigned int*)ws->d_scan_row,
+                                                           (const unsigned long long*)ws->d_scan_key, labels, st, hd);
+        count_launch();
+        err = cudaGetLastError();
+        if (err != cudaSuccess) {
+            snprintf(g_gm_err, sizeof(g_gm_err), "tile-GEMM fix-up launch failed: %s", cudaGetErrorString(err));
+            return 1;
+        }
     }
     return 0;
 }

@@ -50,6 +50,14 @@ struct GemmWorkspace {
     void* d_open = nullptr;  // (row, runner-up | mode) of the rows the TF32 scores did not decide
     size_t open_cap = 0;
     void* d_count = nullptr;
+    // second pass over the rows with more than two candidates: gathered rows, their original index, score
+    // threshold and (distance, index) minimum, and the candidate list
+    void* d_xs = nullptr;
+    void* d_scan_row = nullptr;
+    void* d_scan_thr = nullptr;
+    void* d_scan_key = nullptr;
+    void* d_cand = nullptr;
+    size_t scan_cap = 0, scan_d = 0;
 };
 bool gemm_supported(const float* X, int d, int k);
 size_t gemm_workspace_bytes(int64_t n, int d, int k);
