@@ -258,7 +258,7 @@ def parity_check(torch, h, X, C, cfg):
     d, k = cfg["d"], cfg["k"]
     n = X.shape[0]
     m = int(min(n, max(2000, min(100_000, 3e10 / (k * d)))))
-    idx = torch.linspace(0, n - 1, m, device=X.device).long()
+    idx = torch.arange(m, device=X.device, dtype=torch.int64) * (n // m)  # evenly spaced rows
     rows = X[idx].contiguous()
     lab = h.predict(rows, C)[0].cpu().numpy()
     Xh, Ch = rows.cpu().numpy(), C.cpu().numpy()

@@ -110,11 +110,12 @@ def partitions_to_device(parts: List, device, free_inputs: bool = True, out=None
             evs[slot].synchronize()  # the copy that last used the next buffer has drained
 
         for i, m in enumerate(mats):
-            src_t = torch.from_numpy(m).view(-1)
-            n_el = src_t.numel()
+            n_el = m.size
             if n_el == 0:
                 continue
-            if src_t.is_pinned():
+            # only writable arrays can be views of pinned torch memory (pandas hands out read-only views)
+            src_t = torch.from_numpy(m).view(-1) if m.flags.writeable else None
+            if src_t is not None and src_t.is_pinned():
                 if ring is not None:
                     flush()
                 flat[off:off + n_el].copy_(src_t, non_blocking=True)
