@@ -113,6 +113,7 @@ struct b200km_handle {
     size_t n_cap = 0;
     TcWorkspace tc;
     GemmWorkspace gm;
+    SortedUpdateWorkspace su;
     bool split_only = false;  // this fit saw too many float64 re-decisions in the screen kernel
     int last_kernel = 0;      // 0 = FFMA kernels, 1 = split-TF32 fused kernel, 2 = screen kernel, 3 = tile GEMM
     // instrumentation (b200km_profile_*)
@@ -137,6 +138,7 @@ int free_ws(b200km_handle* h) {
     cudaFree(h->d_work);
     tc_free(&h->tc);
     gemm_free(&h->gm);
+    sorted_update_free(&h->su);
     if (h->h_state) cudaFreeHost(h->h_state);
     if (h->h_scalar) cudaFreeHost(h->h_scalar);
     for (auto& e : h->ev)
@@ -272,8 +274,17 @@ int run_pass(b200km_handle* h, int kind, const float* X, int64_t n, int d, int k
         if (rec) h->prof_n++;
         float* bst = best ? best : h->d_best;
         if (best || (acc && want_inertia)) launch_rowdist(X, n, d, C, lab, bst, s);
-        else if (acc) CU_TRY(cudaMemsetAsync(bst, 0, sizeof(float) * (size_t)n, s));
-        if (acc) launch_update(X, n, d, k, lab, bst, acc, h->d_state, honor_done, s);
+        if (acc) {
+            if (sorted_update_supported(n, d, k)) {
+                // stable sort by label + segmented float64 sums in a fixed order (no atomics on the data)
+                if (sorted_update(&h->su, X, n, d, k, lab, acc, h->d_state, honor_done, s))
+                    return fail("sorted update failed: %s", sorted_update_last_error());
+                if (want_inertia) launch_sum_best(bst, n, acc + (size_t)k * d + k, s);
+            } else {
+                if (!(best || want_inertia)) CU_TRY(cudaMemsetAsync(bst, 0, sizeof(float) * (size_t)n, s));
+                launch_update(X, n, d, k, lab, bst, acc, h->d_state, honor_done, s);
+            }
+        }
         CU_TRY(cudaGetLastError());
         return 0;
     }

@@ -72,4 +72,26 @@ void launch_rowdist(const float* X, int64_t n, int d, const float* C, const int3
 const char* gemm_last_error();
 void gemm_free(GemmWorkspace* ws);
 
+// Deterministic per-cluster sums / counts for large k (kernels_update.cu): stable counting sort of the rows by
+// label + segmented float64 reduction in a fixed order; acc = [k*d sums | k counts | ...], added to.
+struct SortedUpdateWorkspace {
+    void* d_H = nullptr;
+    size_t H_cap = 0;
+    void* d_total = nullptr;
+    size_t total_cap = 0;
+    void* d_start = nullptr;
+    size_t start_cap = 0;
+    void* d_order = nullptr;
+    size_t order_cap = 0;
+    void* d_head = nullptr;
+    size_t head_cap = 0;
+    void* d_tail = nullptr;
+    size_t tail_cap = 0;
+};
+bool sorted_update_supported(int64_t n, int d, int k);
+int sorted_update(SortedUpdateWorkspace* ws, const float* X, int64_t n, int d, int k, const int32_t* labels, double* acc,
+                  IterState* st, bool honor_done, cudaStream_t s);
+const char* sorted_update_last_error();
+void sorted_update_free(SortedUpdateWorkspace* ws);
+
 }  // namespace b200km

@@ -80,6 +80,27 @@ def test_lloyd_step_sums_counts_inertia(handle):
     parity.assert_inertia_close(float(inertia.item()), i_ref)
 
 
+def test_fit_is_bitwise_reproducible(handle):
+    """Labels are exact and the sums are added in one fixed order (stable sort by label + segmented float64
+    reduction): the same fit gives the same bits, run after run."""
+    X, _ = ko.make_blobs(60000, 128, 50, seed=8)
+    init = ko.random_init(X, 700, seed=8)
+    Xd, Cd = dev(X), dev(init)
+    a = handle.fit(Xd, Cd, max_iter=4, tol=0.0)
+    b = handle.fit(Xd, Cd, max_iter=4, tol=0.0)
+    assert torch.equal(a[0], b[0]) and a[1] == b[1]
+    # a label with very many rows (its range spans many segments of the reduction) and empty labels
+    C2 = init.copy()
+    C2[5:] += 1000.0  # nearly everything goes to the first five centroids, most labels stay empty
+    s1 = handle.lloyd_step(Xd, dev(C2), want_labels=True)
+    s2 = handle.lloyd_step(Xd, dev(C2), want_labels=True)
+    assert torch.equal(s1[0], s2[0]) and torch.equal(s1[1], s2[1])
+    lab = s1[3].cpu().numpy()
+    s_own, c_own = ko.accumulate(X, lab, 700)
+    assert np.array_equal(s1[1].cpu().numpy(), c_own)
+    assert np.allclose(s1[0].cpu().numpy(), s_own, rtol=1e-9, atol=1e-9 * np.abs(s_own).max())
+
+
 def test_structureless_data_and_ties(handle):
     """Uniform data (margins of the order of the TF32 error: most rows go through the exact fix-up, many with
     more than two candidates), duplicated centroids (exact ties -> lowest index) and rows equal to a centroid."""
