@@ -62,7 +62,7 @@ struct GmParams {
     int n_sub;     // K sub-chunks of 16 floats
     int ntile;     // N of one MMA (multiple of 64, <= 256)
     int n_ntiles;  // k_pad / ntile
-    int NA, NB, resident;
+    int NA, NB, resident, rotate;
     int b_slot_bytes;
     const float* bt;   // pre-tiled B operand (gemm_prep_kernel)
     const float* cnt;  // pre-tiled norm operand
@@ -534,8 +534,10 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kGmThreads, 1)
     const bool resident = p.resident != 0;
     // Every cluster walks the N-tiles and the K sub-chunks of B in its own rotation: with all clusters in step,
     // the whole chip would ask the same few L2 slices for the same B lines at the same time.
-    const int nt0 = (int)(cluster_id % n_nt);
-    const int sc0 = 2 * (int)((cluster_id / n_nt) % ((n_sub + 1) / 2));  // whole A chunks: even
+    // (Only while B is small: a B operand near the L2 capacity has to be walked in step, so that one cluster's
+    // miss is the others' hit.)
+    const int nt0 = p.rotate ? (int)(cluster_id % n_nt) : 0;
+    const int sc0 = p.rotate ? 2 * (int)((cluster_id / n_nt) % ((n_sub + 1) / 2)) : 0;  // whole A chunks: even
 
     if (warp == 0) {
         // ===================================== TMA producer =====================================
@@ -975,6 +977,7 @@ int gemm_pass(GemmWorkspace* ws, const float* X, int64_t n, int d, int k, const 
     p.NA = pl.NA;
     p.NB = pl.NB;
     p.resident = pl.resident;
+    p.rotate = (2 * (size_t)pl.k_pad * pl.d_pad * 4 <= ((size_t)16 << 20)) ? 1 : 0;
     p.b_slot_bytes = pl.b_slot_bytes;
     p.bt = (const float*)ws->d_b;
     p.cnt = (const float*)ws->d_cn;

@@ -91,8 +91,11 @@ struct ScParams {
     float* xlo;    // [n] ||x - trunc_tf32(x)||^2: likewise
     int xn_compute;
     int32_t* labels;  // may be null
-    unsigned int* info;  // [n] per-row verdict of the screen (see kInfo*): read by screen_fixup_kernel
-    double* acc;      // [k*d | k | 1] or null (labels-only pass)
+    unsigned int* info;  // [n] verdict word of every OPEN row (see kInfo*): read by screen_fixup_kernel
+    unsigned int* open_bits;  // [num_tiles][4]: bit r of word q = row q*32 + r of the tile is open
+    double* acc;      // [k*d | k | 1] or null (labels-only pass); only its non-nullness matters to the kernel
+    double* slots;    // [grid][slot_stride]: every CTA's float64 partial sums | counts | sum ||x||^2
+    int slot_stride;
     IterState* st;
     int honor_done;
     const float* pd;  // [k][k] upper bounds of ||c_a - c_b||
@@ -256,11 +259,6 @@ __device__ __forceinline__ void top3_of_32(const float (&key)[32], float& o1, fl
     o3 = m3[0];
 }
 
-// Exact decision of the rows the screen left open (bit 31 of their info word), straight from HBM: one warp per
-// row, lane = float4 column chunk; FP32 squared differences (no cancellation: their error is ~2^-21 of the
-// distance itself), float64 when even those tie; ties keep the lowest index.  A row whose exact label differs
-// from the provisional one is moved between the float64 sums.  These rows are few (C2: < 1 %), and keeping this
-// code out of the persistent kernel keeps that kernel's instruction stream hot.
 __device__ __forceinline__ float sqdist_f32(const float4* __restrict__ x4, const float4* __restrict__ c4, int nchunks,
                                             int lane) {
     float s = 0.f;
@@ -284,89 +282,167 @@ __device__ __forceinline__ double sqdist_f64(const float* __restrict__ x, const 
     return s;
 }
 
-__global__ void __launch_bounds__(256) screen_fixup_kernel(const float* __restrict__ X, int64_t n, int d, int k,
-                                                           const float* __restrict__ C, const float* __restrict__ pd,
-                                                           const unsigned int* __restrict__ info,
-                                                           int32_t* __restrict__ labels, double* __restrict__ acc,
-                                                           IterState* st, int honor_done) {
-    if (honor_done && st->done) return;
-    const int lane = threadIdx.x & 31;
-    const int64_t warp0 = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
-    const int64_t nwarps = (int64_t)gridDim.x * (blockDim.x >> 5);
+// Exact label of one open row (one warp): FP32 squared differences, float64 when even those tie; ties keep the
+// lowest index.  word = the row's verdict (computed best, runner-up, which centroids to look at).
+__device__ __forceinline__ int exact_label(const float* __restrict__ x, unsigned int word, int d, int k,
+                                           const float* __restrict__ C, const float* __restrict__ pd, int lane) {
     const int nchunks = d >> 2;
-    unsigned int decided = 0;
-    for (int64_t base = warp0 * 32; base < n; base += nwarps * 32) {
-        const int64_t r = base + lane;
-        const unsigned int w = r < n ? info[r] : 0u;
-        unsigned m = __ballot_sync(0xffffffffu, (w & kInfoUnsafe) != 0u);
-        decided += __popc(m);
-        while (m) {
-            const int src = __ffs(m) - 1;
-            m &= m - 1;
-            const unsigned int word = __shfl_sync(0xffffffffu, w, src);
-            const int64_t row = base + src;
-            const int i1 = (int)(word & 255u), i2 = (int)((word >> 8) & 255u);
-            const unsigned int mode = word & (3u << 16);
-            const float* x = X + (size_t)row * d;
-            const float4* x4 = reinterpret_cast<const float4*>(x);
-            int bi;
-            if (mode == kInfoPair) {
-                const int ja = min(i1, i2), jb = max(i1, i2);
-                const float sa = sqdist_f32(x4, reinterpret_cast<const float4*>(C + (size_t)ja * d), nchunks, lane);
-                const float sb = sqdist_f32(x4, reinterpret_cast<const float4*>(C + (size_t)jb * d), nchunks, lane);
-                bi = sb < sa ? jb : ja;
-                if (fabsf(sa - sb) <= 4e-6f * (sa + sb)) {
-                    const double da = sqdist_f64(x, C + (size_t)ja * d, d, lane);
-                    const double db = sqdist_f64(x, C + (size_t)jb * d, d, lane);
-                    bi = db < da ? jb : ja;
-                }
-            } else {
-                // every centroid, or those that can beat the computed best c_1 at all: ||c_1 - c_j|| <= 2 ||x - c_1||
-                float reach = FLT_MAX;
-                if (mode == kInfoReach)
-                    reach = 2.f * sqrtf(sqdist_f32(x4, reinterpret_cast<const float4*>(C + (size_t)i1 * d), nchunks, lane)) * 1.0001f;
-                float f1 = FLT_MAX, f2 = FLT_MAX;
-                bi = i1;
-                for (int j = 0; j < k; ++j) {
-                    if (j != i1 && reach < FLT_MAX && pd[(size_t)i1 * k + j] > reach) continue;
-                    const float sum = sqdist_f32(x4, reinterpret_cast<const float4*>(C + (size_t)j * d), nchunks, lane);
-                    if (sum < f1) {  // ascending index order: ties keep the lowest
-                        f2 = f1;
-                        f1 = sum;
-                        bi = j;
-                    } else {
-                        f2 = fminf(f2, sum);
-                    }
-                }
-                if (f2 < FLT_MAX && (f2 - f1) <= 4e-6f * (f1 + f2)) {
-                    double bd = DBL_MAX;
-                    for (int j = 0; j < k; ++j) {
-                        if (j != i1 && reach < FLT_MAX && pd[(size_t)i1 * k + j] > reach) continue;
-                        const double sum = sqdist_f64(x, C + (size_t)j * d, d, lane);
-                        if (sum < bd) {
-                            bd = sum;
-                            bi = j;
-                        }
-                    }
-                }
-            }
-            if (bi != i1) {
-                if (labels && lane == 0) labels[row] = bi;
-                if (acc) {  // move the row from its provisional cluster to the exact one
-                    for (int i = lane; i < d; i += 32) {
-                        const double v = (double)__ldg(x + i);
-                        atomicAdd(&acc[(size_t)bi * d + i], v);
-                        atomicAdd(&acc[(size_t)i1 * d + i], -v);
-                    }
-                    if (lane == 0) {
-                        atomicAdd(&acc[(size_t)k * d + bi], 1.0);
-                        atomicAdd(&acc[(size_t)k * d + i1], -1.0);
-                    }
-                }
+    const int i1 = (int)(word & 255u), i2 = (int)((word >> 8) & 255u);
+    const unsigned int mode = word & (3u << 16);
+    const float4* x4 = reinterpret_cast<const float4*>(x);
+    int bi;
+    if (mode == kInfoPair) {
+        const int ja = min(i1, i2), jb = max(i1, i2);
+        const float sa = sqdist_f32(x4, reinterpret_cast<const float4*>(C + (size_t)ja * d), nchunks, lane);
+        const float sb = sqdist_f32(x4, reinterpret_cast<const float4*>(C + (size_t)jb * d), nchunks, lane);
+        bi = sb < sa ? jb : ja;
+        if (fabsf(sa - sb) <= 4e-6f * (sa + sb)) {
+            const double da = sqdist_f64(x, C + (size_t)ja * d, d, lane);
+            const double db = sqdist_f64(x, C + (size_t)jb * d, d, lane);
+            bi = db < da ? jb : ja;
+        }
+        return bi;
+    }
+    // every centroid, or those that can beat the computed best c_1 at all: ||c_1 - c_j|| <= 2 ||x - c_1||
+    float reach = FLT_MAX;
+    if (mode == kInfoReach)
+        reach = 2.f * sqrtf(sqdist_f32(x4, reinterpret_cast<const float4*>(C + (size_t)i1 * d), nchunks, lane)) * 1.0001f;
+    float f1 = FLT_MAX, f2 = FLT_MAX;
+    bi = i1;
+    for (int j = 0; j < k; ++j) {
+        if (j != i1 && reach < FLT_MAX && pd[(size_t)i1 * k + j] > reach) continue;
+        const float sum = sqdist_f32(x4, reinterpret_cast<const float4*>(C + (size_t)j * d), nchunks, lane);
+        if (sum < f1) {  // ascending index order: ties keep the lowest
+            f2 = f1;
+            f1 = sum;
+            bi = j;
+        } else {
+            f2 = fminf(f2, sum);
+        }
+    }
+    if (f2 < FLT_MAX && (f2 - f1) <= 4e-6f * (f1 + f2)) {
+        double bd = DBL_MAX;
+        for (int j = 0; j < k; ++j) {
+            if (j != i1 && reach < FLT_MAX && pd[(size_t)i1 * k + j] > reach) continue;
+            const double sum = sqdist_f64(x, C + (size_t)j * d, d, lane);
+            if (sum < bd) {
+                bd = sum;
+                bi = j;
             }
         }
     }
-    if (lane == 0 && decided) atomicAdd(&st->screen_refined, decided);
+    return bi;
+}
+
+// Exact decision of the rows the screen left open, straight from HBM, and their contribution to the sums.
+// Every CTA owns a contiguous range of tiles and walks it in order, kFixTiles tiles at a time: the open rows come
+// from the bitmap (ascending row order), the warps decide them exactly, then thread t adds column t of every such
+// row - in list order - into the CTA's own float64 partial, which goes to the CTA's slot.  No atomics: the sums
+// do not depend on the order in which anything finishes.  These rows are few (C2: ~1 %), and keeping this code
+// out of the persistent kernel keeps that kernel's instruction stream hot.
+constexpr int kFixTiles = 32;
+constexpr int kFixCtasPerSm = 6;
+__global__ void __launch_bounds__(256) screen_fixup_kernel(const float* __restrict__ X, int64_t n, int d, int k,
+                                                           const float* __restrict__ C, const float* __restrict__ pd,
+                                                           const unsigned int* __restrict__ info,
+                                                           const unsigned int* __restrict__ bits, int64_t num_tiles,
+                                                           int32_t* __restrict__ labels, double* __restrict__ slots,
+                                                           int slot_stride, IterState* st, int honor_done) {
+    extern __shared__ double f_acc[];  // [k*d + k] when slots != nullptr
+    // per open row of the chunk: row offset inside the chunk (bits 18+) | the low 18 bits of its verdict word
+    __shared__ unsigned int s_ent[kFixTiles * kTileM];
+    __shared__ unsigned char s_lab[kFixTiles * kTileM];
+    __shared__ int s_warp[4];
+    if (honor_done && st->done) return;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int acc_n = k * d + k;
+    if (slots)
+        for (int i = tid; i < acc_n; i += 256) f_acc[i] = 0.0;
+    const int64_t t0 = num_tiles * (int64_t)blockIdx.x / gridDim.x;
+    const int64_t t1 = num_tiles * (int64_t)(blockIdx.x + 1) / gridDim.x;
+    unsigned int decided = 0;
+    for (int64_t chunk = t0; chunk < t1; chunk += kFixTiles) {
+        const int nt = (int)((t1 - chunk) < kFixTiles ? (t1 - chunk) : kFixTiles);
+        const float* Xc = X + (size_t)chunk * kTileM * d;
+        // ---- the chunk's open rows, in ascending order (their verdict words are fetched here, all at once) ----
+        unsigned int w = 0;
+        if (tid < nt * 4) w = bits[chunk * 4 + tid];
+        int incl = __popc(w);
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int t = __shfl_up_sync(0xffffffffu, incl, o);
+            if (lane >= o) incl += t;
+        }
+        __syncthreads();  // the previous chunk's lists are no longer read
+        if (warp < 4 && lane == 31) s_warp[warp] = incl;
+        __syncthreads();
+        int off = incl - __popc(w);
+        for (int q = 0; q < warp && q < 4; ++q) off += s_warp[q];
+        const int m = s_warp[0] + s_warp[1] + s_warp[2] + s_warp[3];
+        while (w) {
+            const int bpos = __ffs(w) - 1;
+            w &= w - 1;
+            const unsigned int roff = (unsigned int)(tid * 32 + bpos);
+            s_ent[off++] = (roff << 18) | (info[(size_t)chunk * kTileM + roff] & 0x3FFFFu);
+        }
+        __syncthreads();
+        // ---- exact labels: one warp per row ----
+        for (int i = warp; i < m; i += 8) {
+            const unsigned int e = s_ent[i];
+            const unsigned int roff = e >> 18;
+            const int bi = exact_label(Xc + (size_t)roff * d, e & 0x3FFFFu, d, k, C, pd, lane);
+            if (lane == 0) {
+                s_lab[i] = (unsigned char)bi;
+                if (labels && bi != (int)(e & 255u)) labels[(size_t)chunk * kTileM + roff] = bi;
+            }
+        }
+        __syncthreads();
+        // ---- their rows into the partial sums, in list order: thread t owns column t, threads 128.. count ----
+        if (slots) {
+            if (tid < d) {
+                for (int i = 0; i < m; i += 8) {
+                    float v[8];
+                    int l[8];
+#pragma unroll
+                    for (int u = 0; u < 8; ++u) {
+                        const int ii = i + u < m ? i + u : m - 1;
+                        l[u] = s_lab[ii];
+                        v[u] = __ldg(Xc + (size_t)(s_ent[ii] >> 18) * d + tid);
+                    }
+#pragma unroll
+                    for (int u = 0; u < 8; ++u)
+                        if (i + u < m) f_acc[l[u] * d + tid] += (double)v[u];
+                }
+            } else if (tid >= 128 && tid - 128 < k) {
+                int c = 0;
+                for (int i = 0; i < m; ++i) c += (s_lab[i] == tid - 128);
+                f_acc[k * d + tid - 128] += (double)c;
+            }
+        }
+        decided += (unsigned int)m;
+    }
+    if (slots) {
+        __syncthreads();
+        double* slot = slots + (size_t)blockIdx.x * slot_stride;
+        for (int i = tid; i < acc_n; i += 256) slot[i] = f_acc[i];
+        if (tid == 0) slot[acc_n] = 0.0;
+    }
+    if (tid == 0 && decided) atomicAdd(&st->screen_refined, decided);
+}
+
+// acc[i] += sum over the slots of slot[i], in slot order: one warp per element, lane l adds slots l, l+32, ... and
+// the lanes meet in a fixed tree.
+__global__ void __launch_bounds__(256) slot_reduce_kernel(const double* __restrict__ slots, int nslots, int slot_stride,
+                                                          int len, double* __restrict__ acc, IterState* st, int honor_done) {
+    if (honor_done && st->done) return;
+    const int lane = threadIdx.x & 31;
+    const int i = blockIdx.x * 8 + (threadIdx.x >> 5);
+    if (i >= len) return;
+    double t = 0.0;
+    for (int sidx = lane; sidx < nslots; sidx += 32) t += slots[(size_t)sidx * slot_stride + i];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) t += __shfl_down_sync(0xffffffffu, t, o);
+    if (lane == 0) acc[i] += t;
 }
 
 // ||x||^2 and ||x - trunc_tf32(x)||^2 of one row of the tile in `stage` (interleaved partial sums)
@@ -406,13 +482,17 @@ __global__ void __launch_bounds__(kThreads, 1)
     __shared__ int s_perm[2][kTileM + 8];   // sorted position -> low 16 bits: row offset in a full atom
                                             // (r*128 | swizzle); bit 16: first row of its run; bits 17+: label
     __shared__ int s_permT[2][kTileM + 8];  // same for the narrow tail atom (row pitch 64 / 32 bytes)
+    __shared__ double s_sumxn[16];          // per assign warp: sum of ||x||^2 over its rows
     uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
     const uint32_t smem_base = smem_u32(smem);
 
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
     const int S = p.num_stages;
-    const int ND = p.num_d;  // power of two
+    constexpr int ND = kMaxND;  // score buffers (the plan always uses all four)
+    // Ring positions are advanced by increments: the roles below are single instruction streams that run at the
+    // latency of their dependent instructions, and a 64-bit division by a run-time stage count costs hundreds of
+    // cycles on that path.
     const int stage_bytes = p.stage_bytes;
     const int c_block = 2 * p.k_pad * 128;  // bytes of one full-atom block [c_hi rows | c_lo rows]
     const int dcols = p.k_pad;  // TMEM columns of one score buffer (the c_hi and c_lo products add up in place)
@@ -464,6 +544,7 @@ __global__ void __launch_bounds__(kThreads, 1)
 #pragma unroll 1
             for (int i = threadIdx.x; i < p.k * p.d + p.k; i += kThreads) sacc_init[i] = 0.0;
         }
+        if (threadIdx.x < 16) s_sumxn[threadIdx.x] = 0.0;
 #pragma unroll 1
         for (int i = threadIdx.x; i < 2 * 2 * 4 * kHist; i += kThreads) (&s_hist[0][0][0][0])[i] = 0;
 #pragma unroll 1
@@ -518,9 +599,10 @@ __global__ void __launch_bounds__(kThreads, 1)
                     tma_load_2d(smem_base + p.off_c + p.n_full * c_block + part * p.k_pad * p.tail_cols * 4, &tmCt,
                                 c_full, p.n_full * 32, part * p.k_pad);
             int64_t it = 0;
+            int s = 0;
+            uint32_t sph = 0;  // phase of stage s
             for (int64_t tile = first_tile; tile < p.num_tiles; tile += tile_step, ++it) {
-                const int s = (int)(it % S);
-                mbar_wait(x_empty0 + 8u * s, (uint32_t)(((it / S) & 1) ^ 1));
+                mbar_wait(x_empty0 + 8u * s, sph ^ 1u);
                 trace_ev(p, it, 0);
                 mbar_arrive_expect_tx(x_full0 + 8u * s, (uint32_t)stage_bytes);
                 const uint32_t dst = smem_base + s * stage_bytes;
@@ -529,6 +611,10 @@ __global__ void __launch_bounds__(kThreads, 1)
                 if (p.tail_cols)
                     tma_load_2d(dst + p.n_full * kAtomBytes, &tmXt, x_full0 + 8u * s, p.n_full * 32,
                                 (int)(tile * kTileM));
+                if (++s == S) {
+                    s = 0;
+                    sph ^= 1u;
+                }
             }
         }
         __syncwarp();
@@ -552,11 +638,12 @@ __global__ void __launch_bounds__(kThreads, 1)
         const int tail_steps = p.tail_cols >> 3;
         mbar_wait(c_full, 0);
         int64_t it = 0;
+        int s = 0;
+        uint32_t sph = 0;
         for (int64_t tile = first_tile; tile < p.num_tiles; tile += tile_step, ++it) {
-            const int s = (int)(it % S);
             const int db = (int)(it & (ND - 1));
             mbar_wait(d_empty0 + 8u * db, (uint32_t)(((it / ND) & 1) ^ 1));
-            mbar_wait(x_full0 + 8u * s, (uint32_t)((it / S) & 1));
+            mbar_wait(x_full0 + 8u * s, sph);
             tc_fence_after();
             if (lane == 0) trace_ev(p, it, 1);
             const uint32_t d_tmem = tmem_base + (uint32_t)(db * dcols);
@@ -582,16 +669,20 @@ __global__ void __launch_bounds__(kThreads, 1)
                 trace_ev(p, it, 2);
             }
             __syncwarp();
+            if (++s == S) {
+                s = 0;
+                sph ^= 1u;
+            }
         }
     } else if (warp >= kNormWarp0 && warp < kAssignWarp0) {
         // ======================================= row norms ======================================
         if (p.xn_compute) {
             const int row = (warp - kNormWarp0) * 32 + lane;
             float* xn_s = (float*)(smem + p.off_xn);
-            int64_t it = 0;
-            for (int64_t tile = first_tile; tile < p.num_tiles; tile += tile_step, ++it) {
-                const int s = (int)(it % S);
-                mbar_wait(x_full0 + 8u * s, (uint32_t)((it / S) & 1));
+            int s = 0;
+            uint32_t sph = 0;
+            for (int64_t tile = first_tile; tile < p.num_tiles; tile += tile_step) {
+                mbar_wait(x_full0 + 8u * s, sph);
                 const float2 nn = row_norms(p, smem + (size_t)s * stage_bytes, row);
                 const int64_t grow = tile * kTileM + row;
                 if (grow < p.n) {
@@ -602,6 +693,10 @@ __global__ void __launch_bounds__(kThreads, 1)
                 xn_s[(kMaxStages + s) * kTileM + row] = nn.y;
                 __syncwarp();
                 if (lane == 0) mbar_arrive(xn_full0 + 8u * s);
+                if (++s == S) {
+                    s = 0;
+                    sph ^= 1u;
+                }
             }
         }
     } else if (warp >= kAssignWarp0 && (warp < kUpdateWarp0 || !p.acc)) {
@@ -622,10 +717,11 @@ __global__ void __launch_bounds__(kThreads, 1)
         const int sb = g;
 
         double sum_xn = 0.0;
-        for (int64_t it = g;; it += n_groups) {
-            const int64_t tile = first_tile + it * tile_step;
-            if (tile >= p.num_tiles) break;
-            const int s = (int)(it % S);
+        int s = g % S;
+        uint32_t sph = (uint32_t)((g / S) & 1);  // g < 4: cheap, once
+        int64_t tile = first_tile + (int64_t)g * tile_step;
+        const int64_t group_step = (int64_t)n_groups * tile_step;
+        for (int64_t it = g; tile < p.num_tiles; it += n_groups, tile += group_step) {
             const int db = (int)(it & (ND - 1));
             const int64_t grow = tile * kTileM + row;
             const bool valid = grow < p.n;
@@ -644,7 +740,7 @@ __global__ void __launch_bounds__(kThreads, 1)
             // ---- 32 scores at a time into registers; keys D_j = ||x||^2 + ||c_j||^2 - 2 x^.c_j carry the centroid
             // index in their 7 low mantissa bits (a perturbation below 2^-16 |D_j|, covered by the bound) ----
             if (p.xn_compute) {
-                mbar_wait(xn_full0 + 8u * s, (uint32_t)((it / S) & 1));
+                mbar_wait(xn_full0 + 8u * s, sph);
                 xn = xn_s[s * kTileM + row];
                 xl = xn_s[(kMaxStages + s) * kTileM + row];
             }
@@ -703,9 +799,14 @@ __global__ void __launch_bounds__(kThreads, 1)
             // the verdict goes out with the row; unsafe rows keep the computed best as a provisional label (also in
             // the sums) until screen_fixup_kernel has decided them exactly
             if (valid) {
-                p.info[grow] = verdict;
+                if (amb) p.info[grow] = verdict;
                 if (p.labels) p.labels[grow] = label;
                 sum_xn += (double)xn;
+            }
+            {
+                // open rows: one bitmap word per warp and tile (the exact pass finds them without reading a word per row)
+                const unsigned bits = __ballot_sync(0xffffffffu, amb);
+                if (lane == 0) p.open_bits[tile * 4 + q] = bits;
             }
             if (et == 0) trace_ev(p, it, 5);
 
@@ -718,11 +819,12 @@ __global__ void __launch_bounds__(kThreads, 1)
                 mbar_wait(s_empty0 + 8u * sb, (uint32_t)(((it >> 1) & 1) ^ 1));
                 const int hb = (int)((it >> 1) & 1);
                 uint8_t (*hist)[kHist] = s_hist[g][hb];
-                const int bins = p.k + 1;
-                const int bin = valid ? label : p.k;
+                // Rows that are open (the exact pass adds them) or past the end take no part: bin -1.
+                const int bins = p.k;
+                const int bin = (valid && !amb) ? label : -1;
                 const unsigned peers = __match_any_sync(0xffffffffu, bin);
                 const int rank_w = __popc(peers & ((1u << lane) - 1u));
-                if (rank_w == 0) hist[q][bin] = (uint8_t)__popc(peers);
+                if (bin >= 0 && rank_w == 0) hist[q][bin] = (uint8_t)__popc(peers);
                 named_bar_sync(bar_id, 128);
                 int pos, first;
                 // lane = bin
@@ -736,11 +838,11 @@ __global__ void __launch_bounds__(kThreads, 1)
                 }
                 const int excl = incl - tot;
                 const int mine = excl + (q > 0 ? h0 : 0) + (q > 1 ? h1 : 0) + (q > 2 ? h2 : 0);
-                if (q == 0) s_base[sb][lane] = (unsigned short)excl;  // lanes >= bins hold the total (128)
+                if (q == 0) s_base[sb][lane] = (unsigned short)excl;  // lanes >= bins hold the number of placed rows
                 if (q == 0 && lane == 31) s_base[sb][32] = (unsigned short)incl;
-                pos = __shfl_sync(0xffffffffu, mine, bin) + rank_w;
-                first = pos == __shfl_sync(0xffffffffu, excl, bin);
-                {
+                pos = __shfl_sync(0xffffffffu, mine, bin & 31) + rank_w;
+                first = pos == __shfl_sync(0xffffffffu, excl, bin & 31);
+                if (bin >= 0) {
                     // sorted position -> row offset inside an atom (r*pitch | swizzle bits), a first-of-run flag
                     // (bit 16) and the label (bits 17+)
                     const int meta = (first ? (1 << 16) : 0) | (bin << 17);
@@ -759,14 +861,17 @@ __global__ void __launch_bounds__(kThreads, 1)
                 __syncwarp();
                 if (lane == 0) mbar_arrive(x_empty0 + 8u * s);
             }
+            s += n_groups;  // this group's next tile: n_groups stages further round the ring
+            while (s >= S) {
+                s -= S;
+                sph ^= 1u;
+            }
         }
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) {
             sum_xn += __shfl_xor_sync(0xffffffffu, sum_xn, o);
         }
-        if (lane == 0) {
-            if (p.acc && sum_xn != 0.0) atomicAdd(&p.acc[p.k * p.d + p.k], sum_xn);
-        }
+        if (lane == 0 && p.acc) s_sumxn[warp - kAssignWarp0] = sum_xn;
     } else if (warp >= kUpdateWarp0 && p.acc) {
         // ======================================== update ========================================
         // Eight warps; warp u owns the labels [u*k/8, (u+1)*k/8) for the whole kernel, i.e. one contiguous
@@ -817,11 +922,12 @@ __global__ void __launch_bounds__(kThreads, 1)
             }
         };
         int64_t it = 0;
+        int s = 0;
+        uint32_t sph = 0;
         for (int64_t tile = first_tile; tile < p.num_tiles; tile += tile_step, ++it) {
-            const int s = (int)(it % S);
             const int sb = (int)(it & 1);
             mbar_wait(s_full0 + 8u * sb, (uint32_t)((it >> 1) & 1));
-            mbar_wait(x_full0 + 8u * s, (uint32_t)((it / S) & 1));
+            mbar_wait(x_full0 + 8u * s, sph);
             if (ut == 0) trace_ev(p, it, 7);
             const uint8_t* colp = smem + (size_t)s * stage_bytes + col_off;
             // low halves of the perm words = byte offsets inside the atom
@@ -854,14 +960,12 @@ __global__ void __launch_bounds__(kThreads, 1)
             }
             if (lane == 0) trace_ev(p, it, 8 + u);
             if ((it & 7) == 7 || tile + tile_step >= p.num_tiles) fold();  // single (rare) fold site
+            if (++s == S) {
+                s = 0;
+                sph ^= 1u;
+            }
         }
-        named_bar_sync(3, 256);
-        const int acc_n = p.k * p.d + p.k;
-#pragma unroll 1
-        for (int i = ut; i < acc_n; i += 256) {
-            const double v = sacc[i];
-            if (v != 0.0) atomicAdd(&p.acc[i], v);
-        }
+        (void)ut;
     }
 
 #ifdef B200KM_ENABLE_TRACE
@@ -873,6 +977,20 @@ __global__ void __launch_bounds__(kThreads, 1)
 #endif
     tc_fence_before();
     __syncthreads();
+    if (p.acc) {
+        // this CTA's partial sums go to its own slot: the slots are added in a fixed order afterwards
+        // (slot_reduce_kernel), so the result does not depend on which CTA finishes first
+        double* slot = p.slots + (size_t)blockIdx.x * p.slot_stride;
+        const double* sacc = (const double*)(smem + p.off_acc);
+        const int acc_n = p.k * p.d + p.k;
+#pragma unroll 1
+        for (int i = threadIdx.x; i < acc_n; i += kThreads) slot[i] = sacc[i];
+        if (threadIdx.x == 0) {
+            double t = 0.0;
+            for (int w = 0; w < 16; ++w) t += s_sumxn[w];
+            slot[acc_n] = t;
+        }
+    }
     if (warp == 1) {
         asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512));
     }
@@ -979,6 +1097,36 @@ int screen_pass(TcWorkspace* ws, const float* X, int64_t n, int d, int k, const 
         }
         ws->pd_cap = need_pd;
     }
+    const int64_t num_tiles = (n + kTileM - 1) / kTileM;
+    const int acc_n = k * d + k;
+    const int slot_stride = (acc_n + 1 + 7) & ~7;
+    int64_t fix_grid = (num_tiles + kFixTiles - 1) / kFixTiles;
+    if (fix_grid > kNumSMs * kFixCtasPerSm) fix_grid = kNumSMs * kFixCtasPerSm;
+    if (fix_grid < 1) fix_grid = 1;
+    {
+        const size_t need_bits = sizeof(unsigned int) * 4 * (size_t)(num_tiles + 1);
+        if (need_bits > ws->bits_cap) {
+            if (ws->d_bits) cudaFree(ws->d_bits);
+            ws->d_bits = nullptr;
+            ws->bits_cap = 0;
+            if (cudaMalloc(&ws->d_bits, need_bits + need_bits / 8) != cudaSuccess) {
+                snprintf(g_sc_err, sizeof(g_sc_err), "cudaMalloc of %zu bytes for the open-row bitmap failed", need_bits);
+                return 1;
+            }
+            ws->bits_cap = need_bits + need_bits / 8;
+        }
+        const size_t need_slots = acc ? sizeof(double) * (size_t)slot_stride * (size_t)(kNumSMs + kNumSMs * kFixCtasPerSm) : 0;
+        if (need_slots > ws->slots_cap) {
+            if (ws->d_slots) cudaFree(ws->d_slots);
+            ws->d_slots = nullptr;
+            ws->slots_cap = 0;
+            if (cudaMalloc(&ws->d_slots, need_slots) != cudaSuccess) {
+                snprintf(g_sc_err, sizeof(g_sc_err), "cudaMalloc of %zu bytes for the partial-sum slots failed", need_slots);
+                return 1;
+            }
+            ws->slots_cap = need_slots;
+        }
+    }
     CUtensorMap tmX, tmXt, tmC, tmCt;
     const uint32_t full_box = pl.n_full ? 32 : (uint32_t)pl.tail_cols;  // d < 32 with a narrow tail only
     const uint32_t tail_box = pl.tail_cols ? (uint32_t)pl.tail_cols : full_box;
@@ -1018,7 +1166,7 @@ int screen_pass(TcWorkspace* ws, const float* X, int64_t n, int d, int k, const 
     }
     ScParams p;
     p.n = n;
-    p.num_tiles = (n + kTileM - 1) / kTileM;
+    p.num_tiles = num_tiles;
     p.d = d;
     p.k = k;
     p.k_pad = pl.k_pad;
@@ -1034,7 +1182,10 @@ int screen_pass(TcWorkspace* ws, const float* X, int64_t n, int d, int k, const 
     p.xn_compute = xn_compute ? 1 : 0;
     p.labels = labels;
     p.info = info;
+    p.open_bits = (unsigned int*)ws->d_bits;
     p.acc = acc;
+    p.slots = (double*)ws->d_slots;
+    p.slot_stride = slot_stride;
     p.st = st;
     p.honor_done = honor_done ? 1 : 0;
     // Error model (file header).  x is read truncated to TF32; ||x - x^||^2 is computed per row with the row
@@ -1071,12 +1222,18 @@ int screen_pass(TcWorkspace* ws, const float* X, int64_t n, int d, int k, const 
         return 1;
     }
     {
-        int64_t blocks = (n + 255) / 256;
-        if (blocks > kNumSMs * 8) blocks = kNumSMs * 8;
-        if (blocks < 1) blocks = 1;
-        screen_fixup_kernel<<<(unsigned)blocks, 256, 0, s>>>(X, n, d, k, C, (const float*)ws->d_pd, info, labels, acc, st,
-                                                             honor_done ? 1 : 0);
+        // exact pass over the open rows (deterministic per-CTA partials), then all slots in a fixed order
+        double* fix_slots = acc ? (double*)ws->d_slots + (size_t)grid * slot_stride : nullptr;
+        const size_t fsm = acc ? sizeof(double) * (size_t)acc_n : 0;
+        screen_fixup_kernel<<<(unsigned)fix_grid, 256, fsm, s>>>(X, n, d, k, C, (const float*)ws->d_pd, info,
+                                                                (const unsigned int*)ws->d_bits, num_tiles, labels,
+                                                                fix_slots, slot_stride, st, honor_done ? 1 : 0);
         count_launch();
+        if (acc) {
+            slot_reduce_kernel<<<(acc_n + 1 + 7) / 8, 256, 0, s>>>((const double*)ws->d_slots, (int)(grid + fix_grid),
+                                                                  slot_stride, acc_n + 1, acc, st, honor_done ? 1 : 0);
+            count_launch();
+        }
     }
 #ifdef B200KM_ENABLE_TRACE
     if (p.trace) {  // development aid: synchronous dump of CTA 0's per-tile event clocks

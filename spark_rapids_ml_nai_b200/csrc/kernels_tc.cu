@@ -788,8 +788,14 @@ const char* tc_last_error() { return g_tc_err; }
 void tc_free(TcWorkspace* ws) {
     if (ws->d_buf) cudaFree(ws->d_buf);
     if (ws->d_pd) cudaFree(ws->d_pd);
+    if (ws->d_bits) cudaFree(ws->d_bits);
+    if (ws->d_slots) cudaFree(ws->d_slots);
     ws->d_buf = nullptr;
     ws->d_pd = nullptr;
+    ws->d_bits = nullptr;
+    ws->d_slots = nullptr;
+    ws->bits_cap = 0;
+    ws->slots_cap = 0;
     ws->cap = 0;
     ws->pd_cap = 0;
 }

@@ -9,6 +9,10 @@ struct TcWorkspace {
     size_t cap = 0;
     void* d_pd = nullptr;    // [k][k] upper bounds of the pairwise centroid distances (screen kernel)
     size_t pd_cap = 0;
+    void* d_bits = nullptr;  // open-row bitmap of the screen kernel: 4 words per 128-row tile
+    size_t bits_cap = 0;
+    void* d_slots = nullptr;  // per-CTA float64 partial sums of the screen kernel and its exact pass
+    size_t slots_cap = 0;
 };
 
 bool tc_supported(const float* X, int d, int k, bool with_acc);

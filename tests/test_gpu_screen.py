@@ -120,3 +120,23 @@ def test_fit_switches_to_the_split_kernel_when_the_screen_decides_too_little(han
     Xb, _ = ko.make_blobs(100_000, 100, 20, seed=2)
     Cb, _, it, _ = handle.fit(dev(Xb), dev(ko.random_init(Xb, 20, seed=4)), max_iter=8, tol=0.0, want_inertia=False)
     assert handle.screen_stats()[1] == 2
+
+
+def test_same_fit_twice_is_bitwise_identical(handle):
+    """Determinism of the fused pass: every CTA adds its tiles in a fixed order into its own float64 partial, the
+    open rows are added by the exact pass in row order, and the partials are combined in slot order - no atomics on
+    the sums.  The same 4M-row fit therefore gives the same bits, run after run (labels are exact for every row)."""
+    g = torch.Generator(device="cuda").manual_seed(5)
+    n, d, k = 4_000_000, 100, 20
+    centers = torch.rand((k, d), generator=g, device="cuda") * 20 - 10
+    X = torch.randn((n, d), generator=g, device="cuda") * 3.0 + centers[torch.randint(0, k, (n,), generator=g, device="cuda")]
+    init = X[torch.randperm(n, generator=g, device="cuda")[:k]].contiguous()
+    runs = [handle.fit(X, init, max_iter=6, tol=0.0) for _ in range(3)]
+    open_rows, kernel = handle.screen_stats()
+    assert kernel in (1, 2) and open_rows > 0, "wide blobs: the exact pass has rows to decide"
+    for r in runs[1:]:
+        assert torch.equal(r[0], runs[0][0]), "centroids differ between identical runs"
+        assert r[1] == runs[0][1], "inertia differs between identical runs"
+    s1 = handle.lloyd_step(X, init)
+    s2 = handle.lloyd_step(X, init)
+    assert torch.equal(s1[0], s2[0]) and torch.equal(s1[1], s2[1]) and torch.equal(s1[2], s2[2])
