@@ -218,3 +218,118 @@ def random_init(X: np.ndarray, k: int, seed: int = 1) -> np.ndarray:
     rng = np.random.default_rng(seed)
     idx = rng.choice(X.shape[0], size=k, replace=False)
     return np.asarray(X[np.sort(idx)], dtype=np.float32).copy()
+
+
+# ---- k-means|| ("scalable k-means++") initialisation -------------------------------------------------------------
+# The reference hands initMode="k-means||" to the backend as init="scalable-k-means++" with oversampling_factor
+# (python/src/spark_rapids_ml/clustering.py:72,117-119; the default init mode, :290).  The backend's algorithm is
+# Bahmani et al.'s: oversample candidates in a few rounds with probability l*d^2(x)/phi, weight them by the rows
+# they attract, reduce them to k seeds with weighted k-means++.  Its random stream is the backend's own and is
+# not reproducible here, so the restatement fixes one: a counter-based hash keyed by (seed, stream, global row
+# index) - the same keying the CUDA path uses, which makes the result independent of how rows are sharded.
+_M64 = (1 << 64) - 1
+
+
+def _mix64(z):
+    with np.errstate(over="ignore"):
+        z = np.asarray(z, dtype=np.uint64) + np.uint64(0x9E3779B97F4A7C15)
+        z = (z ^ (z >> np.uint64(30))) * np.uint64(0xBF58476D1CE4E5B9)
+        z = (z ^ (z >> np.uint64(27))) * np.uint64(0x94D049BB133111EB)
+        return z ^ (z >> np.uint64(31))
+
+
+def hash64(seed: int, stream: int, counter) -> np.ndarray:
+    """Counter-based 64-bit hash (splitmix64 finaliser, three rounds): the uniform of (seed, stream, counter)."""
+    s = _mix64(np.uint64(seed & _M64))
+    return _mix64(_mix64(s ^ np.uint64(stream)) ^ np.asarray(counter, dtype=np.uint64))
+
+
+def hash_uniform(seed: int, stream: int, counter) -> np.ndarray:
+    """float64 in [0, 1) from the top 53 bits of hash64."""
+    return (hash64(seed, stream, counter) >> np.uint64(11)).astype(np.float64) * (2.0 ** -53)
+
+
+def _sq_dists_to(X: np.ndarray, C: np.ndarray) -> np.ndarray:
+    """min_j ||x_i - c_j||^2 in float64 (blocked)."""
+    out = np.empty(X.shape[0], dtype=np.float64)
+    C64 = C.astype(np.float64)
+    cn = np.einsum("ij,ij->i", C64, C64)
+    for s in range(0, X.shape[0], _ROW_BLOCK):
+        e = min(X.shape[0], s + _ROW_BLOCK)
+        out[s:e] = _block_sqdist(X[s:e].astype(np.float64), C64, cn).min(axis=1)
+    return out
+
+
+def kmeans_parallel_candidates(X: np.ndarray, k: int, seed: int, oversampling: float = 2.0, max_rounds: int = 8):
+    """Global row indices of the k-means|| candidates, in the order they are collected (first the start row,
+    then every round's picks in ascending row order)."""
+    n = X.shape[0]
+    first = int(hash64(seed, 0, 0) % np.uint64(n))
+    cands = [first]
+    dist = _sq_dists_to(X, X[first:first + 1])
+    phi = float(dist.sum())
+    ell = max(1.0, float(oversampling) * k)
+    rounds = int(min(max_rounds, max(1, np.ceil(np.log(max(phi, 2.0))))))
+    rows = np.arange(n, dtype=np.uint64)
+    for r in range(rounds):
+        if phi <= 0.0:
+            break
+        u = hash_uniform(seed, r + 1, rows)
+        ids = np.nonzero(u < ell * dist / phi)[0]
+        if ids.size == 0:
+            continue
+        cands.extend(int(i) for i in ids)
+        dist = np.minimum(dist, _sq_dists_to(X, X[ids]))
+        phi = float(dist.sum())
+    return cands
+
+
+def kmeans_parallel_init(X: np.ndarray, k: int, seed: int, oversampling: float = 2.0) -> np.ndarray:
+    """k initial centres [k, d] float32 (rows of X) by k-means|| + greedy weighted k-means++ over the candidates."""
+    n = X.shape[0]
+    if n < k:
+        raise ValueError(f"k={k} exceeds the number of rows {n}")
+    cands = kmeans_parallel_candidates(X, k, seed, oversampling)
+    m = len(cands)
+    if m < k:  # tiny or degenerate data: top up with further distinct rows, lowest hash first
+        have = set(cands)
+        order = np.argsort(hash64(seed, 99, np.arange(n, dtype=np.uint64)), kind="stable")
+        for i in order:
+            if int(i) not in have:
+                cands.append(int(i))
+                have.add(int(i))
+                if len(cands) == k:
+                    break
+        return np.ascontiguousarray(X[cands], dtype=np.float32)
+    if m == k:
+        return np.ascontiguousarray(X[cands], dtype=np.float32)
+    C32 = np.ascontiguousarray(X[cands], dtype=np.float32)
+    w = np.bincount(assign(X, C32, want_second=False)[0], minlength=m).astype(np.float64)
+    C = C32.astype(np.float64)
+    trials = 2 + int(np.log(k))
+
+    def pick(P, u):
+        return int(min(m - 1, np.searchsorted(P, u * P[-1], side="right")))
+
+    idx = pick(np.cumsum(w), float(hash_uniform(seed, 200, 0)))
+    chosen = [idx]
+    d2 = ((C - C[idx]) ** 2).sum(axis=1)
+    taken = np.zeros(m, dtype=bool)
+    taken[idx] = True
+    for s in range(1, k):
+        P = np.cumsum(w * d2)
+        if P[-1] <= 0.0:
+            idx = int(np.nonzero(~taken)[0][0])
+            dnew = ((C - C[idx]) ** 2).sum(axis=1)
+        else:
+            tries = [pick(P, float(hash_uniform(seed, 1000 + s, t))) for t in range(trials)]
+            best_pot, idx, dnew = None, -1, None
+            for t in tries:
+                dt = ((C - C[t]) ** 2).sum(axis=1)
+                pot = float((w * np.minimum(d2, dt)).sum())
+                if best_pot is None or pot < best_pot:
+                    best_pot, idx, dnew = pot, t, dt
+        chosen.append(idx)
+        taken[idx] = True
+        d2 = np.minimum(d2, dnew)
+    return np.ascontiguousarray(C32[chosen], dtype=np.float32)

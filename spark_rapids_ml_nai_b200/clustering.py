@@ -155,9 +155,8 @@ def _initial_centroids(handle: "_native.Handle", X: Any, cuml_params: Dict[str, 
     if init == "random":
         return handle.init_centroids(X, k, mode=_native.INIT_RANDOM, seed=seed)
     if init in ("k-means||", "scalable-k-means++"):
-        from .init import kmeans_parallel_init
-
-        return kmeans_parallel_init(handle, X, k, seed=seed, oversampling=float(cuml_params.get("oversampling_factor", 2.0)))
+        return handle.init_centroids(X, k, mode=_native.INIT_KMEANS_PARALLEL, seed=seed,
+                                     oversampling=float(cuml_params.get("oversampling_factor", 2.0)))
     raise ValueError(f"Value '{init}' for 'init' param is unsupported")
 
 

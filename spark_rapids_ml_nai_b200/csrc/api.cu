@@ -9,6 +9,7 @@
 #include <nccl.h>
 
 #include <algorithm>
+#include <cmath>
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
@@ -122,6 +123,7 @@ struct b200km_handle {
     cudaEvent_t pev[2 * kProfMax] = {};
     int prof_n = 0;
     unsigned long long launches = 0;
+    int scope_depth = 0;  // nesting of the entry points that count launches (only the outermost adds)
 };
 
 namespace {
@@ -197,9 +199,11 @@ int ensure_ws(b200km_handle* h, int64_t n, int d, int k, bool need_row_bufs) {
 struct LaunchScope {
     b200km_handle* h;
     unsigned long long start;
-    explicit LaunchScope(b200km_handle* hh) : h(hh), start(g_launches) {}
+    explicit LaunchScope(b200km_handle* hh) : h(hh), start(g_launches) {
+        if (h) h->scope_depth++;
+    }
     ~LaunchScope() {
-        if (h) h->launches += g_launches - start;
+        if (h && --h->scope_depth == 0) h->launches += g_launches - start;
     }
 };
 
@@ -297,6 +301,200 @@ int run_pass(b200km_handle* h, int kind, const float* X, int64_t n, int d, int k
     launch_refine(X, n, d, C, k, labels, best, h->d_state, h->d_work, honor_done, s);
     if (acc) launch_update(X, n, d, k, labels, best, acc, h->d_state, honor_done, s);
     CU_TRY(cudaGetLastError());
+    return 0;
+}
+
+// Shard sizes of all ranks (through the communicator), this rank's first global row and the total.
+int gather_sizes(b200km_handle* h, int64_t n_local, int d, int k, std::vector<long long>* sizes, long long* my_off,
+                 long long* total, cudaStream_t s) {
+    sizes->assign(h->nranks, 0);
+    (*sizes)[h->rank] = n_local;
+    if (h->nranks > 1) {
+        if (ensure_ws(h, 0, d, k, false)) return 1;
+        long long* d_sizes = reinterpret_cast<long long*>(h->d_acc);
+        CU_TRY(cudaMemcpyAsync(d_sizes + h->rank, &(*sizes)[h->rank], sizeof(long long), cudaMemcpyHostToDevice, s));
+        NCCL_TRY(g_nccl.AllGather(d_sizes + h->rank, d_sizes, 1, ncclInt64, h->comm, s));
+        CU_TRY(cudaMemcpyAsync(sizes->data(), d_sizes, sizeof(long long) * h->nranks, cudaMemcpyDeviceToHost, s));
+        CU_TRY(cudaStreamSynchronize(s));
+    }
+    *total = 0;
+    *my_off = 0;
+    for (int r = 0; r < h->nranks; ++r) {
+        if (r == h->rank) *my_off = *total;
+        *total += (*sizes)[r];
+    }
+    return 0;
+}
+
+// Temporary device allocations of one initialisation call, released together.
+struct DevPool {
+    std::vector<void*> ptrs;
+    ~DevPool() {
+        for (void* q : ptrs) cudaFree(q);
+    }
+    template <typename T>
+    T* get(size_t count) {
+        void* q = nullptr;
+        if (cudaMalloc(&q, sizeof(T) * (count ? count : 1)) != cudaSuccess) return nullptr;
+        ptrs.push_back(q);
+        return (T*)q;
+    }
+};
+
+}  // namespace
+
+extern "C" int b200km_predict(b200km_handle* h, const float* X, int64_t n, int d, const float* centroids, int k,
+                              int32_t* labels_out, float* min_dist_out, void* stream);
+
+namespace {
+
+// k-means|| ("scalable k-means++"): see kernels_init.cu (the CPU checker restates the same hash keying and rules).
+// Every rank ends with the same k rows in `out`.
+int kmeans_parallel_init(b200km_handle* h, const float* X, int64_t n_local, int d, int k, unsigned long long seed,
+                         double oversampling, float* out, cudaStream_t s) {
+    std::vector<long long> sizes;
+    long long my_off = 0, total = 0;
+    if (gather_sizes(h, n_local, d, k, &sizes, &my_off, &total, s)) return 1;
+    if (total < k) return fail("k=%d exceeds the number of rows %lld", k, total);
+    const double ell = oversampling * k < 1.0 ? 1.0 : oversampling * k;
+    const unsigned int cap = (unsigned int)(8.0 * ell) + 4096u;
+    DevPool pool;
+    float* dist = pool.get<float>((size_t)n_local);
+    float* tmp = pool.get<float>((size_t)n_local);
+    int32_t* lab = pool.get<int32_t>((size_t)n_local);
+    long long* list = pool.get<long long>((size_t)h->nranks * (cap + 1));
+    long long* all = pool.get<long long>((size_t)h->nranks * (cap + 1));
+    unsigned int* cnt = pool.get<unsigned int>(4);
+    double* red = pool.get<double>(1024 + 8);
+    if (!dist || !tmp || !lab || !list || !all || !cnt || !red) return fail("k-means||: device allocation failed");
+    CU_TRY(cudaMemsetAsync(cnt, 0, 16, s));
+
+    std::vector<long long> cands;  // global row indices, in collection order
+    float* cand = nullptr;         // their rows [cands.size(), d]
+    size_t cand_cap = 0;
+
+    auto phi_of = [&](double* phi) -> int {
+        launch_det_sum(dist, n_local, red, red + 1024, cnt + 1, s);
+        if (h->nranks > 1) NCCL_TRY(g_nccl.AllReduce(red + 1024, red + 1024, 1, ncclFloat64, ncclSum, h->comm, s));
+        CU_TRY(cudaMemcpyAsync(phi, red + 1024, sizeof(double), cudaMemcpyDeviceToHost, s));
+        CU_TRY(cudaStreamSynchronize(s));
+        return 0;
+    };
+    // appends the rows `ids` (ascending global indices) to the candidate matrix and folds them into dist
+    auto add = [&](const std::vector<long long>& ids, bool first) -> int {
+        const size_t m0 = cands.size(), m1 = m0 + ids.size();
+        if (m1 > cand_cap) {
+            const size_t want = m1 * 2 + 64;
+            float* bigger = pool.get<float>(want * d);
+            if (!bigger) return fail("k-means||: device allocation of %zu candidate rows failed", want);
+            if (cand) CU_TRY(cudaMemcpyAsync(bigger, cand, sizeof(float) * m0 * d, cudaMemcpyDeviceToDevice, s));
+            cand = bigger;
+            cand_cap = want;
+        }
+        CU_TRY(cudaMemcpyAsync(list, ids.data(), sizeof(long long) * ids.size(), cudaMemcpyHostToDevice, s));
+        float* rows = cand + m0 * d;
+        launch_gather_rows(X, n_local, d, my_off, list, (int)ids.size(), rows, s);
+        if (h->nranks > 1)
+            NCCL_TRY(g_nccl.AllReduce(rows, rows, ids.size() * (size_t)d, ncclFloat32, ncclSum, h->comm, s));
+        cands.insert(cands.end(), ids.begin(), ids.end());
+        if (n_local > 0) {
+            if (b200km_predict(h, X, n_local, d, rows, (int)ids.size(), lab, first ? dist : tmp, s)) return 1;
+            if (!first) launch_min_inplace(dist, tmp, n_local, s);
+        }
+        CU_TRY(cudaGetLastError());
+        return 0;
+    };
+
+    const long long first_row = (long long)(init_hash64(seed, 0, 0) % (unsigned long long)total);
+    if (add({first_row}, true)) return 1;
+    double phi = 0.0;
+    if (phi_of(&phi)) return 1;
+    int rounds = (int)std::ceil(std::log(phi > 2.0 ? phi : 2.0));
+    rounds = rounds < 1 ? 1 : (rounds > 8 ? 8 : rounds);
+    std::vector<long long> host_list(cap), host_all((size_t)h->nranks * (cap + 1));
+    for (int r = 0; r < rounds && phi > 0.0; ++r) {
+        CU_TRY(cudaMemsetAsync(cnt, 0, sizeof(unsigned int), s));
+        launch_kpar_sample(dist, n_local, my_off, seed, r + 1, ell / phi, list + 1, cnt, cap, s);
+        unsigned int count = 0;
+        CU_TRY(cudaMemcpyAsync(&count, cnt, sizeof(unsigned int), cudaMemcpyDeviceToHost, s));
+        CU_TRY(cudaStreamSynchronize(s));
+        if (count > cap) return fail("k-means||: a sampling round picked %u rows (capacity %u): oversampling factor too large", count, cap);
+        CU_TRY(cudaMemcpyAsync(host_list.data(), list + 1, sizeof(long long) * count, cudaMemcpyDeviceToHost, s));
+        CU_TRY(cudaStreamSynchronize(s));
+        std::sort(host_list.begin(), host_list.begin() + count);  // the append order is arbitrary: ascending rows
+        std::vector<long long> ids;
+        if (h->nranks > 1) {
+            // every rank contributes [count | ids ...]; ranks own ascending row ranges, so rank order is row order
+            std::vector<long long> seg((size_t)cap + 1, 0);
+            seg[0] = count;
+            std::copy(host_list.begin(), host_list.begin() + count, seg.begin() + 1);
+            CU_TRY(cudaMemcpyAsync(all + (size_t)h->rank * (cap + 1), seg.data(), sizeof(long long) * (cap + 1), cudaMemcpyHostToDevice, s));
+            NCCL_TRY(g_nccl.AllGather(all + (size_t)h->rank * (cap + 1), all, (size_t)cap + 1, ncclInt64, h->comm, s));
+            CU_TRY(cudaMemcpyAsync(host_all.data(), all, sizeof(long long) * host_all.size(), cudaMemcpyDeviceToHost, s));
+            CU_TRY(cudaStreamSynchronize(s));
+            for (int q = 0; q < h->nranks; ++q) {
+                const long long* sg = host_all.data() + (size_t)q * (cap + 1);
+                ids.insert(ids.end(), sg + 1, sg + 1 + sg[0]);
+            }
+        } else {
+            ids.assign(host_list.begin(), host_list.begin() + count);
+        }
+        if (ids.empty()) continue;
+        if (add(ids, false)) return 1;
+        if (phi_of(&phi)) return 1;
+    }
+
+    const size_t m = cands.size();
+    if (m < (size_t)k) {
+        // tiny or degenerate data: further distinct rows, lowest hash first (the same rule on every rank)
+        if (total > (1ll << 27)) return fail("k-means||: fewer candidates than k on %lld rows", total);
+        std::unordered_set<long long> have(cands.begin(), cands.end());
+        std::vector<std::pair<unsigned long long, long long>> order;
+        order.reserve((size_t)total);
+        for (long long g = 0; g < total; ++g)
+            if (!have.count(g)) order.emplace_back(init_hash64(seed, 99, (unsigned long long)g), g);
+        const size_t need = (size_t)k - m;
+        std::partial_sort(order.begin(), order.begin() + need, order.end());
+        // ties of the 64-bit hash are not expected; the (hash, row) pair order makes the rule total anyway
+        for (size_t i = 0; i < need; ++i) {
+            if (add({order[i].second}, false)) return 1;
+        }
+        CU_TRY(cudaMemcpyAsync(out, cand, sizeof(float) * (size_t)k * d, cudaMemcpyDeviceToDevice, s));
+        CU_TRY(cudaStreamSynchronize(s));
+        return 0;
+    }
+    if (m == (size_t)k) {
+        CU_TRY(cudaMemcpyAsync(out, cand, sizeof(float) * (size_t)k * d, cudaMemcpyDeviceToDevice, s));
+        CU_TRY(cudaStreamSynchronize(s));
+        return 0;
+    }
+    // weights: rows nearest to each candidate
+    unsigned long long* counts = pool.get<unsigned long long>(m);
+    if (!counts) return fail("k-means||: device allocation failed");
+    CU_TRY(cudaMemsetAsync(counts, 0, sizeof(unsigned long long) * m, s));
+    if (n_local > 0) {
+        if (b200km_predict(h, X, n_local, d, cand, (int)m, lab, nullptr, s)) return 1;
+        launch_label_count(lab, n_local, counts, s);
+    }
+    if (h->nranks > 1) NCCL_TRY(g_nccl.AllReduce(counts, counts, m, ncclUint64, ncclSum, h->comm, s));
+    std::vector<unsigned long long> hc(m);
+    CU_TRY(cudaMemcpyAsync(hc.data(), counts, sizeof(unsigned long long) * m, cudaMemcpyDeviceToHost, s));
+    CU_TRY(cudaStreamSynchronize(s));
+    std::vector<double> hw(m);
+    for (size_t j = 0; j < m; ++j) hw[j] = (double)hc[j];
+    const int trials = 2 + (int)std::floor(std::log((double)k));
+    double* w = pool.get<double>(m);
+    double* P = pool.get<double>(m);
+    double* d2 = pool.get<double>(m);
+    double* Dt = pool.get<double>((size_t)trials * m);
+    unsigned char* taken = pool.get<unsigned char>(m);
+    int* chosen = pool.get<int>((size_t)k);
+    void* state = pool.get<unsigned char>(kpp_state_bytes());
+    if (!w || !P || !d2 || !Dt || !taken || !chosen || !state) return fail("k-means||: device allocation failed");
+    CU_TRY(cudaMemcpyAsync(w, hw.data(), sizeof(double) * m, cudaMemcpyHostToDevice, s));
+    run_weighted_kmeanspp(cand, (int)m, d, k, w, seed, trials > 16 ? 16 : trials, P, d2, Dt, taken, chosen, state, out, s);
+    CU_TRY(cudaGetLastError());
+    CU_TRY(cudaStreamSynchronize(s));
     return 0;
 }
 
@@ -582,11 +780,13 @@ int b200km_init_centroids(b200km_handle* h, const float* X, int64_t n_local, int
                           uint64_t seed, double oversampling, float* centroids_out, void* stream) {
     if (check_shape(h, X, n_local, d, k)) return 1;
     if (!centroids_out) return fail("centroids_out is null");
-    (void)oversampling;
     cudaStream_t s = (cudaStream_t)stream;
     CU_TRY(cudaSetDevice(h->device));
-    if (mode != B200KM_INIT_RANDOM)
-        return fail("init mode %d is not implemented in the C ABI (k-means|| runs in the Python host layer)", mode);
+    LaunchScope scope(h);
+    if (mode == B200KM_INIT_KMEANS_PARALLEL)
+        return kmeans_parallel_init(h, X, n_local, d, k, (unsigned long long)seed, oversampling > 0.0 ? oversampling : 2.0,
+                                    centroids_out, s);
+    if (mode != B200KM_INIT_RANDOM) return fail("unknown init mode %d", mode);
     // every rank learns all shard sizes, draws the same k distinct global rows, and contributes the
     // rows it owns; a float sum all-reduce of the otherwise-zero [k,d] buffer assembles the result.
     std::vector<long long> sizes(h->nranks, 0);

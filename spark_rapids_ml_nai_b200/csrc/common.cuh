@@ -61,4 +61,19 @@ void launch_sum_best(const float* best, int64_t n, double* out, cudaStream_t s);
 void launch_finalize(float* C, int k, int d, float* cnorm, double* acc, double* shift_part, double* cnt_part,
                      double tol, IterState* st, IterState* snap, cudaStream_t s);
 
+// ---- k-means|| initialisation, kernels_init.cu ---------------------------------------------------
+unsigned long long init_hash64(unsigned long long seed, unsigned long long stream, unsigned long long counter);
+double init_hash_uniform(unsigned long long seed, unsigned long long stream, unsigned long long counter);
+void launch_kpar_sample(const float* dist, int64_t n, long long row0, unsigned long long seed, int stream, double scale,
+                        long long* list, unsigned int* count, unsigned int cap, cudaStream_t s);
+void launch_min_inplace(float* dist, const float* other, int64_t n, cudaStream_t s);
+void launch_det_sum(const float* x, int64_t n, double* partial, double* out, unsigned int* ticket, cudaStream_t s);
+void launch_gather_rows(const float* X, int64_t n, int d, long long row0, const long long* ids, int m, float* out,
+                        cudaStream_t s);
+void launch_label_count(const int32_t* labels, int64_t n, unsigned long long* counts, cudaStream_t s);
+size_t kpp_state_bytes();
+void run_weighted_kmeanspp(const float* C, int m, int d, int k, const double* w, unsigned long long seed, int trials,
+                           double* P, double* d2, double* Dt, unsigned char* taken, int* chosen, void* state, float* out,
+                           cudaStream_t s);
+
 }  // namespace b200km

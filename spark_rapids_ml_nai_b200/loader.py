@@ -13,7 +13,7 @@ from typing import List, Optional, Sequence
 import numpy as np
 
 _STAGE_BYTES = 128 << 20
-_COPY_THREADS = 4
+_COPY_THREADS = 8
 _staging = {}
 _pool = None
 
@@ -94,14 +94,24 @@ def partitions_to_device(parts: List, device, free_inputs: bool = True, out=None
         ring = None
         slot = 0
         off = 0          # elements of X already scheduled
-        fill = 0         # elements staged in the current slot, not yet sent
+        fill = 0         # elements assigned to the current slot, not yet sent
         cap = _STAGE_BYTES // 4
+        pending = []     # copy tasks of the current slot: (dst view, src view)
 
         def flush():
-            nonlocal fill, off, slot
+            nonlocal fill, off, slot, pending
             if fill == 0:
                 return
             bufs, evs = ring
+            # the slot's batches are copied by the worker threads side by side (NumPy releases the GIL inside a
+            # copy): Arrow-sized batches are a few MB each, far too small to split individually
+            if len(pending) == 1:
+                _parallel_copy(*pending[0])
+            else:
+                pool = _copy_pool()
+                for f in [pool.submit(np.copyto, dst, src) for dst, src in pending]:
+                    f.result()
+            pending = []
             flat[off:off + fill].copy_(bufs[slot].view(torch.float32)[:fill], non_blocking=True)
             evs[slot].record(stream)
             off += fill
@@ -123,7 +133,7 @@ def partitions_to_device(parts: List, device, free_inputs: bool = True, out=None
                 mats[i] = None
                 continue
             # pageable memory: small (Arrow-sized) batches are packed into a 128 MB pinned slot and leave as one
-            # host -> device copy; while that copy is in flight the next slot is filled by the copy threads
+            # host -> device copy; while that copy is in flight the next slot is filled
             if ring is None:
                 ring = _staging_ring(device.index or 0)
                 ring[1][slot].synchronize()
@@ -132,7 +142,7 @@ def partitions_to_device(parts: List, device, free_inputs: bool = True, out=None
             while done < n_el:
                 take = min(n_el - done, cap - fill)
                 stage = ring[0][slot].numpy().view(np.float32)
-                _parallel_copy(stage[fill:fill + take], src[done:done + take])
+                pending.append((stage[fill:fill + take], src[done:done + take]))
                 fill += take
                 done += take
                 if fill == cap:

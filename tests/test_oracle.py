@@ -105,3 +105,19 @@ def test_ambiguous_mask_and_single_cluster():
     X = np.arange(12, dtype=np.float32).reshape(4, 3)
     res = ko.lloyd_fit(X, X[:1], max_iter=5, tol=1e-20)
     assert np.allclose(res.centers[0], X.mean(axis=0)) and np.isinf(res.second).all()
+
+
+def test_kmeans_parallel_restatement_properties():
+    """The oracle's k-means|| (initMode's default, python/src/spark_rapids_ml/clustering.py:290): k distinct rows of
+    X, reproducible, one seed per blob on separated blobs, and independent of how the rows would be sharded (its
+    random numbers are a function of the global row index)."""
+    X, centers = ko.make_blobs(20000, 16, 10, seed=4)
+    a = ko.kmeans_parallel_init(X, 10, seed=7)
+    assert np.array_equal(a, ko.kmeans_parallel_init(X, 10, seed=7))
+    assert not np.array_equal(a, ko.kmeans_parallel_init(X, 10, seed=8))
+    rows = {tuple(r) for r in X}
+    assert a.shape == (10, 16) and all(tuple(r) in rows for r in a) and len({tuple(r) for r in a}) == 10
+    assert sorted(ko.predict(a, centers).tolist()) == list(range(10)), "one seed in every blob"
+    u = ko.hash_uniform(5, 3, np.arange(100000, dtype=np.uint64))
+    assert 0.0 <= u.min() and u.max() < 1.0 and abs(u.mean() - 0.5) < 0.01
+    assert int(ko.hash64(7, 1, 0)) == 8075172986249684972  # pins the hash (the CUDA path must produce the same stream)
