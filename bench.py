@@ -403,7 +403,7 @@ def run_config(torch, dist, _native, h, name, args, steps, warmup, world, rank, 
         "ms_per_step": ms_max / steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
         "dtype": "f32", "data": "synthetic",
         "config": {"workload": cfg["desc"], "rows_total": rows_total, "rows_per_gpu": n_local, "d": d, "k": k,
-                   "path": path, "init": "random rows (seed 1), identical on all ranks", "tol": 0.0,
+                   "path": path, "allreduce": h.last_reduce() if is_fit else "none (predict shards need no exchange)", "init": "random rows (seed 1), identical on all ranks", "tol": 0.0,
                    "data_keying": "row values are a function of the global row index (one seed per 2^20-row chunk)",
                    "l2": f"per-GPU input {n_local * d * 4 / 1e9:.2f} GB " +
                          ("is larger than the 126 MB L2, no flush needed" if n_local * d * 4 > 4e8

@@ -80,6 +80,13 @@ int b200km_set_path(b200km_handle* h, int path);
 /* Name of the path the last compute call on this handle used ("ffma" / "tc" / "gemm"). */
 const char* b200km_last_path(b200km_handle* h);
 
+/* How the per-iteration sums of the last b200km_fit on this handle crossed the GPUs: "none" (one rank),
+ * "nvlink-oneshot" (small accumulators: every rank stores its [k*d | k | 1] float64 block into its slot of every
+ * peer's exchange buffer - CUDA IPC mappings set up by b200km_create - and adds the slots in rank order inside the
+ * fused finalize kernel) or "nccl" (ncclAllReduce: large accumulators, or when the peer mappings could not be made).
+ * The reference's two FP32 all-reduces per iteration happen inside cuML; diagnostics only. */
+const char* b200km_last_reduce(b200km_handle* h);
+
 /* 1 when the fused tcgen05 kernel can run this (d, k): with_update != 0 asks for the fit pass
  * (assignment + float64 accumulation), 0 for the assignment-only pass.  Diagnostics; no counterpart
  * in the reference. */

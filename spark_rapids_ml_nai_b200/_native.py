@@ -27,6 +27,7 @@ _SIGNATURES = {
     "b200km_abort": (_c.c_int, [_c.c_void_p]),
     "b200km_set_path": (_c.c_int, [_c.c_void_p, _c.c_int]),
     "b200km_last_path": (_c.c_char_p, [_c.c_void_p]),
+    "b200km_last_reduce": (_c.c_char_p, [_c.c_void_p]),
     "b200km_tc_supported": (_c.c_int, [_c.c_int, _c.c_int, _c.c_int]),
     "b200km_profile_enable": (_c.c_int, [_c.c_void_p, _c.c_int]),
     "b200km_profile_read": (_c.c_int, [_c.c_void_p, _c.POINTER(_c.c_double), _c.POINTER(_c.c_int),
@@ -159,6 +160,10 @@ class Handle:
 
     def last_path(self) -> str:
         return load().b200km_last_path(self._h).decode()
+
+    def last_reduce(self) -> str:
+        """"none" / "nvlink-oneshot" / "nccl": how the last fit's sums crossed the GPUs."""
+        return load().b200km_last_reduce(self._h).decode()
 
     def profile_enable(self, on: bool = True) -> None:
         _check(load().b200km_profile_enable(self._h, 1 if on else 0))

@@ -124,11 +124,21 @@ struct b200km_handle {
     int prof_n = 0;
     unsigned long long launches = 0;
     int scope_depth = 0;  // nesting of the entry points that count launches (only the outermost adds)
+    // one-shot all-reduce over NVLink for small accumulators (fused into finalize): this rank's exchange buffer
+    // and every peer's, mapped through CUDA IPC at creation; NCCL does the large messages and the bootstrap
+    unsigned char* xr_local = nullptr;
+    unsigned char* xr_peer[16] = {};
+    bool xr_ok = false;
+    unsigned int fit_serial = 0;
+    const char* last_reduce = "none";
 };
 
 namespace {
 
 int free_ws(b200km_handle* h) {
+    for (int r = 0; r < 16; ++r)
+        if (h->xr_peer[r] && h->xr_peer[r] != h->xr_local) cudaIpcCloseMemHandle(h->xr_peer[r]);
+    if (h->xr_local) cudaFree(h->xr_local);
     cudaFree(h->d_state);
     cudaFree(h->d_acc);
     cudaFree(h->d_shift);
@@ -193,6 +203,52 @@ int ensure_ws(b200km_handle* h, int64_t n, int d, int k, bool need_row_bufs) {
         h->n_cap = want;
     }
     return 0;
+}
+
+// Maps every rank's exchange buffer into this process (CUDA IPC handles travel through one ncclAllGather).
+// The ranks then agree (ncclAllReduce MIN) on whether all of them succeeded; if not, nobody uses the buffers.
+void setup_exchange(b200km_handle* h) {
+    int ok = 1;
+    cudaIpcMemHandle_t mine;
+    unsigned char* d_handles = nullptr;
+    std::vector<cudaIpcMemHandle_t> all(h->nranks);
+    if (cudaMalloc((void**)&h->xr_local, kXrBytes) != cudaSuccess || cudaMemset(h->xr_local, 0, kXrBytes) != cudaSuccess ||
+        cudaIpcGetMemHandle(&mine, h->xr_local) != cudaSuccess ||
+        cudaMalloc((void**)&d_handles, sizeof(cudaIpcMemHandle_t) * h->nranks + 16) != cudaSuccess)
+        ok = 0;
+    cudaGetLastError();
+    if (d_handles) {
+        // the collectives must run on every rank even when this one failed locally
+        if (ok) cudaMemcpy(d_handles + sizeof(mine) * h->rank, &mine, sizeof(mine), cudaMemcpyHostToDevice);
+        if (g_nccl.AllGather(d_handles + sizeof(mine) * h->rank, d_handles, sizeof(mine), ncclChar, h->comm, 0) != ncclSuccess) ok = 0;
+        if (cudaStreamSynchronize(0) != cudaSuccess) ok = 0;
+        if (ok) cudaMemcpy(all.data(), d_handles, sizeof(mine) * h->nranks, cudaMemcpyDeviceToHost);
+    }
+    if (ok) {
+        for (int r = 0; r < h->nranks; ++r) {
+            if (r == h->rank) {
+                h->xr_peer[r] = h->xr_local;
+                continue;
+            }
+            void* ptr = nullptr;
+            if (cudaIpcOpenMemHandle(&ptr, all[r], cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) {
+                ok = 0;
+                cudaGetLastError();
+                break;
+            }
+            h->xr_peer[r] = (unsigned char*)ptr;
+        }
+    }
+    if (d_handles) {
+        int* d_ok = reinterpret_cast<int*>(d_handles + sizeof(mine) * h->nranks);
+        cudaMemcpy(d_ok, &ok, sizeof(int), cudaMemcpyHostToDevice);
+        int agreed = 0;
+        if (g_nccl.AllReduce(d_ok, d_ok, 1, ncclInt32, ncclMin, h->comm, 0) == ncclSuccess &&
+            cudaStreamSynchronize(0) == cudaSuccess && cudaMemcpy(&agreed, d_ok, sizeof(int), cudaMemcpyDeviceToHost) == cudaSuccess)
+            h->xr_ok = agreed == 1;
+        cudaFree(d_handles);
+    }
+    cudaGetLastError();
 }
 
 // Adds the kernel launches issued inside its scope (counted at the launch sites) to the handle's counter.
@@ -575,6 +631,7 @@ int b200km_create(int device, int rank, int nranks, const void* uid128, b200km_h
             return fail("ncclCommInitRank failed: %s", g_nccl.GetErrorString(r));
         }
     }
+    if (nranks > 1 && nranks <= 16) setup_exchange(h);  // failure leaves NCCL in charge of every reduction
     *out = h;
     return 0;
 }
@@ -605,6 +662,8 @@ int b200km_set_path(b200km_handle* h, int path) {
 }
 
 const char* b200km_last_path(b200km_handle* h) { return h ? h->last_path : "none"; }
+
+const char* b200km_last_reduce(b200km_handle* h) { return h ? h->last_reduce : "none"; }
 
 int b200km_tc_supported(int d, int k, int with_update) {
     return tc_supported(nullptr, d, k, with_update != 0) ? 1 : 0;
@@ -679,6 +738,10 @@ int b200km_fit(b200km_handle* h, const float* X, int64_t n_local, int d, int k, 
     const int64_t acc_len = (int64_t)kd + k + 1;
 
     h->split_only = false;
+    // small accumulators: one CTA does the all-reduce (NVLink peer stores, rank-ordered sum) and the centroid update
+    const bool fused_tail = finalize_fused_supported(k, d) && (h->nranks == 1 || h->xr_ok) && max_iter < (1 << 20);
+    const unsigned int epoch0 = (++h->fit_serial) << 20;
+    h->last_reduce = h->nranks == 1 ? "none" : (fused_tail ? "nvlink-oneshot" : "nccl");
     CU_TRY(cudaMemcpyAsync(h->d_C, init_centroids, sizeof(float) * kd, cudaMemcpyDeviceToDevice, s));
     if (kind == KIND_FFMA) launch_rownorm(X, n_local, d, h->d_xnorm, s);
     launch_prep(h->d_C, k, d, h->d_cnorm, h->d_acc, acc_len, h->d_state, true, s);
@@ -696,10 +759,15 @@ int b200km_fit(b200km_handle* h, const float* X, int64_t n_local, int d, int k, 
             if (!h->split_only && (double)h->h_state[slot].screen_refined > 0.02 * seen) h->split_only = true;
         }
         if (run_pass(h, kind, X, n_local, d, k, h->d_C, nullptr, nullptr, h->d_acc, true, it == 0, s)) return 1;
-        if (h->nranks > 1)
-            NCCL_TRY(g_nccl.AllReduce(h->d_acc, h->d_acc, (size_t)acc_len, ncclFloat64, ncclSum, h->comm, s));
-        launch_finalize(h->d_C, k, d, h->d_cnorm, h->d_acc, h->d_shift, h->d_shift + h->k_cap, tol, h->d_state,
-                        h->d_state + 1 + slot, s);
+        if (fused_tail) {
+            launch_finalize_fused(h->d_C, k, d, h->d_cnorm, h->d_acc, tol, h->d_state, h->d_state + 1 + slot,
+                                  h->nranks > 1 ? h->xr_peer : nullptr, h->rank, h->nranks, epoch0 + (unsigned int)it + 1u, s);
+        } else {
+            if (h->nranks > 1)
+                NCCL_TRY(g_nccl.AllReduce(h->d_acc, h->d_acc, (size_t)acc_len, ncclFloat64, ncclSum, h->comm, s));
+            launch_finalize(h->d_C, k, d, h->d_cnorm, h->d_acc, h->d_shift, h->d_shift + h->k_cap, tol, h->d_state,
+                            h->d_state + 1 + slot, s);
+        }
         CU_TRY(cudaGetLastError());
         // the host looks at the state kRing iterations later; the copy rides a side stream so that the next
         // pass starts right behind finalize
@@ -720,6 +788,12 @@ int b200km_fit(b200km_handle* h, const float* X, int64_t n_local, int d, int k, 
         if (h->nranks > 1)
             NCCL_TRY(g_nccl.AllReduce(d_inertia, d_inertia, 1, ncclFloat64, ncclSum, h->comm, s));
         CU_TRY(cudaMemcpyAsync(h->h_scalar, d_inertia, sizeof(double), cudaMemcpyDeviceToHost, s));
+    }
+    else if (fused_tail && h->nranks > 1 && max_iter > 0) {
+        // no collective follows the loop: one tiny all-reduce keeps a fast rank's next fit from writing into an
+        // exchange buffer a slow rank is still reading
+        CU_TRY(cudaMemsetAsync(d_inertia, 0, sizeof(double), s));
+        NCCL_TRY(g_nccl.AllReduce(d_inertia, d_inertia, 1, ncclFloat64, ncclSum, h->comm, s));
     }
     CU_TRY(cudaMemcpyAsync(centroids_out, h->d_C, sizeof(float) * kd, cudaMemcpyDeviceToDevice, s));
     CU_TRY(cudaMemcpyAsync(&h->h_state[kRing], h->d_state, sizeof(IterState), cudaMemcpyDeviceToHost, s));

@@ -61,6 +61,16 @@ void launch_sum_best(const float* best, int64_t n, double* out, cudaStream_t s);
 void launch_finalize(float* C, int k, int d, float* cnorm, double* acc, double* shift_part, double* cnt_part,
                      double tol, IterState* st, IterState* snap, cudaStream_t s);
 
+// Fused tail for small k*d (kernels_generic.cu): one-shot all-reduce over NVLink peer stores + centroid update in
+// one CTA.  Exchange buffer of a rank: [2 parities][nranks <= 16][kXrDoubles] float64, then the arrival flags.
+constexpr int kXrDoubles = 8192;
+constexpr size_t kXrFlagOff = (size_t)2 * 16 * kXrDoubles * sizeof(double);
+constexpr size_t kXrBytes = kXrFlagOff + 2 * 16 * sizeof(unsigned int);
+bool finalize_fused_supported(int k, int d);
+// peer_bases: every rank's exchange buffer as mapped in this process (nullptr when nranks == 1)
+void launch_finalize_fused(float* C, int k, int d, float* cnorm, double* acc, double tol, IterState* st, IterState* snap,
+                           unsigned char* const* peer_bases, int rank, int nranks, unsigned int epoch, cudaStream_t s);
+
 // ---- k-means|| initialisation, kernels_init.cu ---------------------------------------------------
 unsigned long long init_hash64(unsigned long long seed, unsigned long long stream, unsigned long long counter);
 double init_hash_uniform(unsigned long long seed, unsigned long long stream, unsigned long long counter);
