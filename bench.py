@@ -43,7 +43,8 @@ CONFIGS = {
 FIT_METRIC, FIT_UNIT = "kmeans_fit_rows_iters_per_s", "rows*iters/s"
 PRED_METRIC, PRED_UNIT = "kmeans_predict_rows_per_s", "rows/s"
 CHUNK_ROWS = 1 << 20
-KERNELS = {0: "assign_ffma_kernel", 1: "kmeans_fused_tc_kernel", 2: "kmeans_screen_kernel", 3: "kmeans_gemm_kernel"}
+KERNELS = {0: "assign_ffma_kernel", 1: "kmeans_fused_tc_kernel", 2: "kmeans_screen_kernel", 3: "kmeans_gemm_kernel",
+           4: "kmeans_small_fit_kernel"}
 NO_SPARK = "pyspark.ml baseline not runnable on this box: no JVM/pyspark in image"
 
 
@@ -55,7 +56,7 @@ def parse_args():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--config", default="c2", choices=sorted(CONFIGS))
     ap.add_argument("--rows", type=int, default=0, help="override total rows (debug only; marks the line)")
-    ap.add_argument("--path", default="auto", choices=["auto", "ffma", "tc", "tc_split", "gemm"])
+    ap.add_argument("--path", default="auto", choices=["auto", "ffma", "tc", "tc_split", "gemm", "small"])
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-also", action="store_true", help="skip the other BASELINE.json configurations")
@@ -368,7 +369,13 @@ def run_config(torch, dist, _native, h, name, args, steps, warmup, world, rank, 
     work = rows_total * steps
     value = work / (ms_max * 1e-3)
     path = h.last_path()
-    roofline = roofline_of(cfg, n_local, kern_ms / max(1, kern_n), kern_n, last_kernel, refined_rows, steps, peaks)
+    kms = kern_ms / max(1, kern_n)
+    if last_kernel == 4:
+        kms /= steps  # one launch runs every iteration: report the kernel time per iteration
+    roofline = roofline_of(cfg, n_local, kms, kern_n, last_kernel, refined_rows, steps, peaks)
+    if roofline and last_kernel == 4:
+        roofline["note"] = ("one cooperative launch runs all iterations with the shard resident in shared memory: no HBM "
+                            "traffic per iteration, kernel_ms is the launch time / iterations (latency-bound config)")
 
     # ---- result fingerprint: identical for every world size (the data is a function of the global row index)
     if is_fit:
@@ -510,7 +517,7 @@ def main():
         uid = obj[0]
     h = _native.Handle(device=local_rank, rank=rank, nranks=world, uid=uid)
     h.set_path({"auto": _native.PATH_AUTO, "ffma": _native.PATH_FFMA, "tc": _native.PATH_TC,
-                "tc_split": _native.PATH_TC_SPLIT, "gemm": _native.PATH_GEMM}[args.path])
+                "tc_split": _native.PATH_TC_SPLIT, "gemm": _native.PATH_GEMM, "small": _native.PATH_SMALL}[args.path])
     peaks = load_peaks()
 
     sampler = ClockSampler(local_rank) if rank == 0 else None

@@ -44,6 +44,10 @@ typedef struct b200km_handle b200km_handle;
                                   TF32 screen + exact fix-up, sums by a separate pass; AUTO takes it when k*d is
                                   beyond the fused kernels' shared memory */
 
+#define B200KM_PATH_SMALL 5    /* b200km_fit only, one rank: the shard stays in the shared memory of all SMs and one
+                                  cooperative kernel runs every Lloyd iteration (float64 distances, one grid barrier
+                                  per iteration); AUTO takes it for small shards with k*d <= 512 */
+
 /* init modes for b200km_init_centroids; reference: clustering.py:72 ("initMode" -> "init"),
  * values "random" and "k-means||" (clustering.py:185-186, tests/test_kmeans.py:84,93). */
 #define B200KM_INIT_RANDOM 0
@@ -77,7 +81,7 @@ int b200km_abort(b200km_handle* h);
  * not support makes the next compute call fail rather than fall back. */
 int b200km_set_path(b200km_handle* h, int path);
 
-/* Name of the path the last compute call on this handle used ("ffma" / "tc" / "gemm"). */
+/* Name of the path the last compute call on this handle used ("ffma" / "tc" / "gemm" / "small"). */
 const char* b200km_last_path(b200km_handle* h);
 
 /* How the per-iteration sums of the last b200km_fit on this handle crossed the GPUs: "none" (one rank),

@@ -126,6 +126,8 @@ struct b200km_handle {
     int scope_depth = 0;  // nesting of the entry points that count launches (only the outermost adds)
     // one-shot all-reduce over NVLink for small accumulators (fused into finalize): this rank's exchange buffer
     // and every peer's, mapped through CUDA IPC at creation; NCCL does the large messages and the bootstrap
+    double* d_small = nullptr;  // slots of the shared-memory resident fit
+    size_t small_cap = 0;
     unsigned char* xr_local = nullptr;
     unsigned char* xr_peer[16] = {};
     bool xr_ok = false;
@@ -139,6 +141,7 @@ int free_ws(b200km_handle* h) {
     for (int r = 0; r < 16; ++r)
         if (h->xr_peer[r] && h->xr_peer[r] != h->xr_local) cudaIpcCloseMemHandle(h->xr_peer[r]);
     if (h->xr_local) cudaFree(h->xr_local);
+    cudaFree(h->d_small);
     cudaFree(h->d_state);
     cudaFree(h->d_acc);
     cudaFree(h->d_shift);
@@ -656,7 +659,7 @@ int b200km_abort(b200km_handle* h) {
 
 int b200km_set_path(b200km_handle* h, int path) {
     if (!h) return fail("null handle");
-    if (path < B200KM_PATH_AUTO || path > B200KM_PATH_GEMM) return fail("unknown path %d", path);
+    if (path < B200KM_PATH_AUTO || path > B200KM_PATH_SMALL) return fail("unknown path %d", path);
     h->path = path;
     return 0;
 }
@@ -731,11 +734,41 @@ int b200km_fit(b200km_handle* h, const float* X, int64_t n_local, int d, int k, 
     cudaStream_t s = (cudaStream_t)stream;
     CU_TRY(cudaSetDevice(h->device));
     LaunchScope scope(h);
+    const size_t kd = (size_t)k * d;
+    const int64_t acc_len = (int64_t)kd + k + 1;
+    {
+        // latency regime: a shard that fits the shared memory of all SMs runs the whole fit in one cooperative kernel
+        const bool can_small = h->nranks == 1 && small_fit_supported(n_local, d, k);
+        if (h->path == B200KM_PATH_SMALL && !can_small)
+            return fail("shared-memory resident fit forced but not available for n=%lld d=%d k=%d (one rank, k*d + k <= 2047, "
+                        "the shard within the SMs' shared memory)", (long long)n_local, d, k);
+        if (h->path == B200KM_PATH_SMALL || (h->path == B200KM_PATH_AUTO && can_small && kd <= 512)) {
+            if (ensure_ws(h, n_local, d, k, false)) return 1;
+            const size_t need = small_slots_bytes(n_local, d, k) / sizeof(double);
+            if (grow(&h->d_small, &h->small_cap, need)) return 1;
+            const bool rec = h->prof && h->prof_n < b200km_handle::kProfMax;
+            if (rec) CU_TRY(cudaEventRecord(h->pev[2 * h->prof_n], s));
+            double* d_inertia = h->d_acc + kd + k;
+            if (small_fit(X, n_local, d, k, init_centroids, max_iter, tol, h->d_small, h->d_C, labels_out,
+                          inertia_out ? d_inertia : nullptr, h->d_state, s))
+                return fail("resident fit failed: %s", small_last_error());
+            if (rec) CU_TRY(cudaEventRecord(h->pev[2 * h->prof_n + 1], s));
+            if (rec) h->prof_n++;
+            h->last_path = "small";
+            h->last_kernel = 4;
+            h->last_reduce = "none";
+            if (inertia_out) CU_TRY(cudaMemcpyAsync(h->h_scalar, d_inertia, sizeof(double), cudaMemcpyDeviceToHost, s));
+            CU_TRY(cudaMemcpyAsync(centroids_out, h->d_C, sizeof(float) * kd, cudaMemcpyDeviceToDevice, s));
+            CU_TRY(cudaMemcpyAsync(&h->h_state[kRing], h->d_state, sizeof(IterState), cudaMemcpyDeviceToHost, s));
+            CU_TRY(cudaStreamSynchronize(s));
+            if (n_iter_out) *n_iter_out = h->h_state[kRing].n_iter;
+            if (inertia_out) *inertia_out = h->h_scalar[0];
+            return 0;
+        }
+    }
     int kind = KIND_FFMA;
     if (pick_path(h, X, d, k, true, &kind)) return 1;
     if (ensure_ws(h, n_local, d, k, true)) return 1;
-    const size_t kd = (size_t)k * d;
-    const int64_t acc_len = (int64_t)kd + k + 1;
 
     h->split_only = false;
     // small accumulators: one CTA does the all-reduce (NVLink peer stores, rank-ordered sum) and the centroid update

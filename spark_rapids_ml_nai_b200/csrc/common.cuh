@@ -71,6 +71,13 @@ bool finalize_fused_supported(int k, int d);
 void launch_finalize_fused(float* C, int k, int d, float* cnorm, double* acc, double tol, IterState* st, IterState* snap,
                            unsigned char* const* peer_bases, int rank, int nranks, unsigned int epoch, cudaStream_t s);
 
+// ---- shared-memory resident whole-fit kernel for small shards, kernels_small.cu -------------------------------
+bool small_fit_supported(int64_t n, int d, int k);
+size_t small_slots_bytes(int64_t n, int d, int k);
+int small_fit(const float* X, int64_t n, int d, int k, const float* init, int max_iter, double tol, double* slots,
+              float* C_out, int32_t* labels_out, double* inertia_out, IterState* st, cudaStream_t s);
+const char* small_last_error();
+
 // ---- k-means|| initialisation, kernels_init.cu ---------------------------------------------------
 unsigned long long init_hash64(unsigned long long seed, unsigned long long stream, unsigned long long counter);
 double init_hash_uniform(unsigned long long seed, unsigned long long stream, unsigned long long counter);
