@@ -22,7 +22,7 @@ with open(f"profiles/{tag}_launches_summary.md", "w") as f:
     f.write(f"Per-launch times are cold-cache and serialised: compare SHARES. The raw list is `{tag}_launches.csv`.\n\n| kernel | launches | total ms | share |\n|---|---|---|---|\n")
     for name, (n, ms) in sorted(agg.items(), key=lambda kv: -kv[1][1]):
         f.write(f"| `{name[:150]}` | {n} | {ms:.3f} | {100 * ms / tot:.1f}% |\n")
-    lib = [(n, v) for n, v in agg.items() if "b200km" in n]
+    lib = [(n, v) for n, v in agg.items() if "b200km" in n] or list(agg.items())  # a -k filtered list is all library
     lt = sum(v[1] for _, v in lib)
     f.write("\nLibrary kernels only (everything `at::` is bench.py's synthetic data generation, outside the timed region):\n\n| kernel | launches | total ms | share of library time |\n|---|---|---|---|\n")
     for name, (n, ms) in sorted(lib, key=lambda kv: -kv[1][1]):
