@@ -157,7 +157,7 @@ def gen_blobs_device(torch, lo, hi, d, k, seed, device):
 def sample_for_cpu(cfg, budget_flops=4e10):
     """(rows, iterations) of the bounded CPU sample of a configuration."""
     rows_total, d, k = cfg["rows"], cfg["d"], cfg["k"]
-    iters = 1 if cfg["kind"] == "predict" else (4 if k * d <= 4000 else 2)
+    iters = 1 if cfg["kind"] == "predict" else (10 if k * d <= 4000 else 2)
     rows = int(min(rows_total, max(2000, budget_flops / (2.0 * k * d * iters))))
     if k * d <= 4000:
         rows = min(rows_total, 2_000_000)

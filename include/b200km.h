@@ -132,6 +132,8 @@ int b200km_fit(b200km_handle* h, const float* X, int64_t n_local, int d, int k,
 /* One assignment + accumulation pass over this rank's rows (no all-reduce, no update):
  * sums_out device float64 [k*d], counts_out device float64 [k], inertia_out device float64 [1]
  * (sum of squared distances to `centroids`), labels_out device int32 [n] or NULL.
+ * The inertia comes from per-row distances (FP32 differences on the fused small-k path, which costs it one more
+ * pass over X), never from a cancelling sum-of-squares identity.
  * Building block of b200km_fit exposed for tests and the benchmark; it is the per-iteration
  * device work of `KMeansMG.fit` (clustering.py:367-370). */
 int b200km_lloyd_step(b200km_handle* h, const float* X, int64_t n, int d, int k,
@@ -145,8 +147,14 @@ int b200km_predict(b200km_handle* h, const float* X, int64_t n, int d, const flo
                    int k, int32_t* labels_out, float* min_dist_out, void* stream);
 
 /* Chooses k initial centroids from the (row-sharded) data and leaves the same [k,d] array on
- * every rank in `centroids_out` (device).  mode: B200KM_INIT_RANDOM or
- * B200KM_INIT_KMEANS_PARALLEL (oversampling = cuML's oversampling_factor, clustering.py:119).
+ * every rank in `centroids_out` (device).  Collective: every rank calls it with its shard.
+ * mode B200KM_INIT_RANDOM: k distinct global rows (Floyd sampling, mt19937_64(seed)); `oversampling` is ignored.
+ * mode B200KM_INIT_KMEANS_PARALLEL: k-means|| (scalable k-means++), all on the device: one random start row, then
+ * up to 8 rounds that pick every row with probability oversampling*k*d^2(x)/phi (oversampling = cuML's
+ * oversampling_factor, clustering.py:119; <= 0 means 2.0), the picks gathered over NCCL, the candidates weighted by
+ * the rows they attract and reduced to k seeds by greedy weighted k-means++.  Its random numbers are a
+ * counter-based hash of (seed, stream, GLOBAL row index): the result is the same for every sharding of the rows.
+ * The returned centroids are rows of X.  Synchronises `stream` several times.
  * Replaces the `init=` handling inside `KMeansMG.fit` (clustering.py:72,117,355-359). */
 int b200km_init_centroids(b200km_handle* h, const float* X, int64_t n_local, int d, int k,
                           int mode, uint64_t seed, double oversampling, float* centroids_out,

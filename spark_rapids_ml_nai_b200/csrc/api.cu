@@ -126,6 +126,7 @@ struct b200km_handle {
     int scope_depth = 0;  // nesting of the entry points that count launches (only the outermost adds)
     // one-shot all-reduce over NVLink for small accumulators (fused into finalize): this rank's exchange buffer
     // and every peer's, mapped through CUDA IPC at creation; NCCL does the large messages and the bootstrap
+    double* d_red = nullptr;    // scratch of the fixed-order sums
     double* d_small = nullptr;  // slots of the shared-memory resident fit
     size_t small_cap = 0;
     unsigned char* xr_local = nullptr;
@@ -142,6 +143,7 @@ int free_ws(b200km_handle* h) {
         if (h->xr_peer[r] && h->xr_peer[r] != h->xr_local) cudaIpcCloseMemHandle(h->xr_peer[r]);
     if (h->xr_local) cudaFree(h->xr_local);
     cudaFree(h->d_small);
+    cudaFree(h->d_red);
     cudaFree(h->d_state);
     cudaFree(h->d_acc);
     cudaFree(h->d_shift);
@@ -853,9 +855,17 @@ int b200km_lloyd_step(b200km_handle* h, const float* X, int64_t n, int d, int k,
     CU_TRY(cudaGetLastError());
     h->split_only = false;
     if (n > 0) {
-        if (run_pass(h, kind, X, n, d, k, centroids, labels_out, nullptr, h->d_acc, false, true, s, true)) return 1;
+        int32_t* lab = labels_out ? labels_out : h->d_labels;
+        if (run_pass(h, kind, X, n, d, k, centroids, lab, nullptr, h->d_acc, false, true, s, true)) return 1;
         if (h->last_kernel == 2) {
-            screen_inertia_fix(centroids, k, d, h->d_acc, s);
+            // The screen kernel produces no per-row distances.  The inertia could be rebuilt from the sums
+            // (sum ||x||^2 - 2 sum c.S + sum n ||c||^2), but that form cancels for data far from the origin; one more
+            // pass takes exact FP32 differences per row instead, added in a fixed order.
+            if (!h->d_red && cudaMalloc((void**)&h->d_red, sizeof(double) * 1040) != cudaSuccess) return fail("cudaMalloc failed");
+            unsigned int* ticket = reinterpret_cast<unsigned int*>(h->d_red + 1032);
+            CU_TRY(cudaMemsetAsync(ticket, 0, sizeof(unsigned int), s));
+            launch_rowdist(X, n, d, centroids, lab, h->d_best, s);
+            launch_det_sum(h->d_best, n, h->d_red, h->d_acc + kd + k, ticket, s);
         }
     }
     CU_TRY(cudaMemcpyAsync(sums_out, h->d_acc, sizeof(double) * kd, cudaMemcpyDeviceToDevice, s));

@@ -20,8 +20,9 @@
 // those tie) and moves a row between the float64 sums when its exact label differs - labels and sums are exact
 // for every row.  Keeping that rarely executed code out of the persistent kernel matters: inside it, one such
 // row cost 1400-2400 cycles of an assign warp (instruction fetch of cold code), 0.9 % of the rows cost 30 %.
-// The inertia of the pass follows from the float64 sums:
-//   sum_i ||x_i - c_l(i)||^2 = sum_i ||x_i||^2 - 2 sum_j c_j.S_j + sum_j n_j ||c_j||^2     (screen_inertia_fix).
+// The pass produces no per-row distances; a caller that wants the inertia of the pass (b200km_lloyd_step) takes one
+// more pass of exact per-row differences (rowdist_kernel) rather than the cancelling identity
+// sum ||x||^2 - 2 sum c.S + sum n ||c||^2.
 //
 // When too many rows stay open (structureless data) b200km_fit switches to the split-TF32 kernel
 // (kernels_tc.cu), which also splits x and therefore leaves nothing open beyond FP32 rounding.
@@ -201,30 +202,6 @@ __global__ void __launch_bounds__(128) screen_prep_kernel(const float* __restric
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
     if (lane == 0) pd[pair] = sqrtf(s) * (1.f + 1e-5f) + 1e-30f;
-}
-
-// acc[k*d + k] (which holds sum_i ||x_i||^2 after the screen kernel) += sum_j (n_j ||c_j||^2 - 2 c_j.S_j),
-// all in float64 from the pass's own sums: the exact inertia of the pass's labels against `C`.
-__global__ void __launch_bounds__(256) screen_inertia_fix_kernel(const float* __restrict__ C, int k, int d,
-                                                                 double* __restrict__ acc) {
-    __shared__ double red[8];
-    double t = 0.0;
-    const size_t kd = (size_t)k * d;
-    for (size_t idx = threadIdx.x; idx < kd; idx += blockDim.x) {
-        const double c = (double)C[idx];
-        const double cnt = acc[kd + idx / d];
-        t += c * (cnt * c - 2.0 * acc[idx]);
-    }
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) t += __shfl_xor_sync(0xffffffffu, t, o);
-    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = t;
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        double s = 0.0;
-        for (int w = 0; w < 8; ++w) s += red[w];
-        const double v = acc[kd + k] + s;
-        acc[kd + k] = v > 0.0 ? v : 0.0;
-    }
 }
 
 // The three smallest of 32 keys by a tournament of sorted lists (independent operations, short dependency
@@ -1061,11 +1038,6 @@ size_t screen_workspace_bytes(int d, int k) {
     return pl.ok ? sizeof(float) * (2 * (size_t)pl.k_pad * pl.d_pad + (size_t)k * k) : 0;
 }
 const char* screen_last_error() { return g_sc_err; }
-
-void screen_inertia_fix(const float* C, int k, int d, double* acc, cudaStream_t s) {
-    screen_inertia_fix_kernel<<<1, 256, 0, s>>>(C, k, d, acc);
-    count_launch();
-}
 
 int screen_pass(TcWorkspace* ws, const float* X, int64_t n, int d, int k, const float* C, const float* cnorm,
                 float* xnorm, float* xlo, unsigned int* info, bool xn_compute, int32_t* labels, double* acc,

@@ -33,14 +33,12 @@ void launch_split_centroids(const float* C, int k, int d, int k_pad, int d_pad, 
 
 // Screen kernel (kernels_screen.cu): the same pass with the TF32 view of X read by the tensor cores straight
 // from shared memory, a rigorous error band and a float64 re-decision inside it.  Produces labels (optional)
-// and, when acc != nullptr, sums / counts and sum_i ||x_i||^2 in the inertia slot (screen_inertia_fix turns
-// that slot into the pass's inertia).  No per-row distances.
+// and, when acc != nullptr, sums / counts and sum_i ||x_i||^2 in the inertia slot.  No per-row distances.
 bool screen_supported(const float* X, int d, int k, bool with_acc);
 size_t screen_workspace_bytes(int d, int k);
 int screen_pass(TcWorkspace* ws, const float* X, int64_t n, int d, int k, const float* C, const float* cnorm,
                 float* xnorm, float* xlo, unsigned int* info, bool xn_compute, int32_t* labels, double* acc,
                 IterState* st, bool honor_done, cudaStream_t s);
-void screen_inertia_fix(const float* C, int k, int d, double* acc, cudaStream_t s);
 const char* screen_last_error();
 void tc_free(TcWorkspace* ws);
 

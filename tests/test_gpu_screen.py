@@ -140,3 +140,16 @@ def test_same_fit_twice_is_bitwise_identical(handle):
     s1 = handle.lloyd_step(X, init)
     s2 = handle.lloyd_step(X, init)
     assert torch.equal(s1[0], s2[0]) and torch.equal(s1[1], s2[1]) and torch.equal(s1[2], s2[2])
+
+
+def test_inertia_of_a_step_far_from_the_origin(handle):
+    """Blobs shifted by 1e3: ||x||^2 is ~1e6 times the cluster distances, a sum-of-squares identity would lose the
+    inertia to cancellation; the step's inertia comes from per-row differences and stays within 1e-4."""
+    X, _ = ko.make_blobs(30000, 100, 20, seed=13)
+    X = (X + 1000.0).astype(np.float32)
+    C = ko.random_init(X, 20, seed=13)
+    sums, counts, inertia, labels = handle.lloyd_step(dev(X), dev(C), want_labels=True)
+    _, _, i_ref, l_ref = ko.lloyd_step(X, C)
+    _, best, second = ko.assign(X, C)
+    parity.assert_labels_match(labels.cpu().numpy(), best, second, l_ref)
+    parity.assert_inertia_close(float(inertia.item()), i_ref)
