@@ -10,7 +10,8 @@ import os
 from typing import Optional, Tuple
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "lib", "libb200km.so")
+# B200KM_LIB: development override (same-box A/B timing of two builds, tools/ab_build.sh)
+LIB_PATH = os.environ.get("B200KM_LIB") or os.path.join(_HERE, "lib", "libb200km.so")
 
 PATH_AUTO, PATH_FFMA, PATH_TC, PATH_TC_SPLIT, PATH_GEMM, PATH_SMALL = 0, 1, 2, 3, 4, 5
 INIT_RANDOM, INIT_KMEANS_PARALLEL = 0, 1

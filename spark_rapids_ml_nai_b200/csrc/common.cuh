@@ -6,6 +6,7 @@
 namespace b200km {
 
 // ---- device-resident iteration state (one per handle) -----------------------------------------
+constexpr int kOwnBinsFirst = 8, kOwnBinsLater = 12;
 struct IterState {
     int done;            // set by finalize when shift^2 < tol
     int n_iter;          // executed Lloyd iterations
@@ -14,9 +15,11 @@ struct IterState {
     double shift2;       // sum_j ||c_new_j - c_old_j||^2 of the last executed iteration
     float cnorm_max;     // max_j ||c_j||^2 of the current centroids
     unsigned int screen_refined;  // rows the screen kernel re-decided in float64 since the last prep
-    // k <= 32: labels owned by each of the 8 update warps of the screen kernel (4 slots per warp, -1 = none).
-    // Contiguous ranges after a centroid preparation; rebalanced by cluster size after every Lloyd iteration.
-    signed char own[32];
+    // k <= 32: labels owned by each update warp of the screen kernel (4 slots per warp, -1 = none), for own_bins
+    // warps: 8 contiguous ranges after a centroid preparation (the first pass of a fit also computes the row norms
+    // and has 8 update warps), 12 warps balanced by cluster size after every Lloyd iteration.
+    signed char own[48];
+    int own_bins;
 };
 
 // Near-tie band: a row whose best and second-best approximate scores differ by less than

@@ -95,10 +95,12 @@ __global__ void __launch_bounds__(128) cnorm_kernel(const float* __restrict__ C,
             st->cnorm_max = fmaxf(fmaxf(red[0], red[1]), fmaxf(red[2], red[3]));
             st->amb_count = 0;
             st->screen_refined = 0;
-            for (int u = 0; u < 8; ++u) {
+            for (int u = 0; u < 12; ++u) {
                 const int lo = (u * k) >> 3, hi = ((u + 1) * k) >> 3;
-                for (int li = 0; li < 4; ++li) st->own[u * 4 + li] = (k <= 32 && lo + li < hi) ? (signed char)(lo + li) : (signed char)-1;
+                for (int li = 0; li < 4; ++li)
+                    st->own[u * 4 + li] = (u < 8 && k <= 32 && lo + li < hi) ? (signed char)(lo + li) : (signed char)-1;
             }
+            st->own_bins = kOwnBinsFirst;
             if (reset_iter) {
                 st->done = 0;
                 st->n_iter = 0;
@@ -503,13 +505,20 @@ __global__ void __launch_bounds__(128) finalize_kernel(float* __restrict__ C, in
             // update-warp ownership for the next pass: largest cluster first onto the least loaded warp with a
             // free slot (the per-tile update time follows the rows a warp owns).  Lane = cluster: the largest
             // remaining one by a warp max, the assignment by lane 0; everything stays in registers / shared.
-            __shared__ signed char s_own[32];
+            __shared__ signed char s_own[48];
             if (threadIdx.x < 32) {
                 const int lane = threadIdx.x;
                 s_own[lane] = (signed char)-1;
+                if (lane < 16) s_own[32 + lane] = (signed char)-1;
                 double mine = lane < k ? ((volatile double*)cnt_part)[lane] : -1.0;
-                double load[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-                int used[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+                double load[kOwnBinsLater];
+                int used[kOwnBinsLater];
+#pragma unroll
+                for (int u = 0; u < kOwnBinsLater; ++u) {
+                    load[u] = 0.0;
+                    used[u] = 0;
+                }
+                __syncwarp();
                 for (int r = 0; r < k; ++r) {
                     // arg max over the lanes, ties to the lowest cluster index
                     double bc = mine;
@@ -526,7 +535,7 @@ __global__ void __launch_bounds__(128) finalize_kernel(float* __restrict__ C, in
                     if (lane == best) mine = -1.0;
                     int w = -1;
 #pragma unroll
-                    for (int u = 0; u < 8; ++u)
+                    for (int u = 0; u < kOwnBinsLater; ++u)
                         if (used[u] < 4 && (w < 0 || load[u] < load[w])) w = u;
                     if (lane == 0) s_own[w * 4 + used[w]] = (signed char)best;
                     used[w] += 1;
@@ -534,6 +543,8 @@ __global__ void __launch_bounds__(128) finalize_kernel(float* __restrict__ C, in
                 }
                 __syncwarp();
                 st->own[lane] = s_own[lane];
+                if (lane < 16) st->own[32 + lane] = s_own[32 + lane];
+                if (lane == 0) st->own_bins = kOwnBinsLater;
             }
         }
         // a stable copy for the host: it is read asynchronously, while later iterations already change *st
@@ -646,8 +657,8 @@ __global__ void __launch_bounds__(1024) finalize_fused_kernel(float* __restrict_
         if (shift2 < tol) st->done = 1;
     }
     if (k <= 32 && warp == 0) {
-        // update-warp ownership for the next pass: clusters sorted by size (bitonic, descending; ties by index)
-        // and dealt to the 8 warps in boustrophedon order - the per-tile update time follows the rows a warp owns
+        // update-warp ownership for the next pass: clusters sorted by size (bitonic, descending; ties by index),
+        // then placed greedily - the per-tile update time follows the rows a warp owns
         double key = lane < k ? s_cnt[lane] : -1.0;
         int idx = lane;
 #pragma unroll
@@ -666,12 +677,34 @@ __global__ void __launch_bounds__(1024) finalize_fused_kernel(float* __restrict_
                 }
             }
         }
-        // lane p now holds the p-th largest cluster
-        const int round = lane >> 3, pos = lane & 7;
-        const int w = (round & 1) ? 7 - pos : pos;
+        // lane p now holds the p-th largest cluster: largest first onto the least loaded warp with a free slot
+        // (lane w < 12 keeps warp w's load and slot count; the choice is a minimum over those lanes)
         st->own[lane] = (signed char)-1;
+        if (lane < 16) st->own[32 + lane] = (signed char)-1;
+        if (lane == 0) st->own_bins = kOwnBinsLater;
         __syncwarp();
-        if (lane < k) st->own[w * 4 + round] = (signed char)idx;
+        double load = 0.0;
+        int used = 0;
+        for (int pth = 0; pth < k; ++pth) {
+            const double sz = __shfl_sync(0xffffffffu, key, pth);
+            const int id = __shfl_sync(0xffffffffu, idx, pth);
+            double cand = (lane < kOwnBinsLater && used < 4) ? load : 1e300;
+            int who = lane;
+#pragma unroll
+            for (int o = 8; o > 0; o >>= 1) {
+                const double oc = __shfl_xor_sync(0xffffffffu, cand, o);
+                const int ow = __shfl_xor_sync(0xffffffffu, who, o);
+                if (oc < cand || (oc == cand && ow < who)) {
+                    cand = oc;
+                    who = ow;
+                }
+            }
+            if (lane < kOwnBinsLater && lane == who) {
+                st->own[lane * 4 + used] = (signed char)id;
+                used += 1;
+                load += sz;
+            }
+        }
     }
     __syncthreads();
     if (tid == 0 && snap) *snap = *st;

@@ -14,8 +14,9 @@
 //      when its runner-up margin exceeds the pair's bound and either no other centroid is that close to c_1
 //      (each centroid's nearest-neighbour distances) or the third-best margin exceeds 4 ||x - x^|| r_1 + eps.
 //      Every row leaves a verdict word; the open rows keep the computed best as a provisional label;
-//   3. sorts the tile's rows by label and adds them (exact FP32 data, not the TF32 view) into per-cluster
-//      sums held in registers / float64 shared memory.
+//   3. adds the decided rows (exact FP32 data, not the TF32 view) into per-cluster sums: the assign warps leave one
+//      mask word per (label, warp), the update warps turn the masks of the labels they own into row lists and add
+//      the rows in ascending order into FP32 registers / float64 shared memory.
 // screen_fixup_kernel then decides the open rows exactly from HBM (FP32 squared differences, float64 when even
 // those tie) and moves a row between the float64 sums when its exact label differs - labels and sums are exact
 // for every row.  Keeping that rarely executed code out of the persistent kernel matters: inside it, one such
@@ -29,11 +30,17 @@
 //
 // Warp roles (704 threads, 1 CTA per SM, grid = #SMs):
 //   warp 0       TMA producer (centroids once, then X tiles: 32-float SWIZZLE_128B K-atoms + a narrow tail)
-//   warp 1       TMEM allocator + MMA issuer (warp-uniform loop, one elected lane, A and B via UMMA descriptors)
-//   warps 2-5    row norms ||x||^2 and ||x - x^||^2 (first pass of a fit only; later passes read them back)
+//   warp 1       TMEM allocator + MMA issuer (warp-uniform loop, one elected lane, A and B via UMMA descriptors);
+//                k_pad <= 64: ONE instruction per K-step against [c_hi ; c_lo] stacked as 2 k_pad columns (the tile is
+//                read from shared memory once), the assign warps add the two halves
+//   warps 2-5    row norms ||x||^2 and ||x - x^||^2 on the first pass of a fit; later passes read them back and
+//                these warps are four more update warps
 //   warps 6-13   assign, two groups taking alternate tiles: tcgen05.ld, three smallest scores by a tournament,
-//                verdict, stable counting sort of the tile by label
-//   warps 14-21  update: label-sorted accumulation; a warp owns <= 4 labels, lane = float4 column chunk
+//                verdict, label masks (shared-memory atomic OR: order-free)
+//   warps 14-21  update: a warp owns <= 4 labels, lane = float4 column chunk
+// What bounds the kernel is how long a tile occupies its shared-memory stage (3 stages at d = 100): every role is a
+// short dependent instruction stream, so the code is kept small (the roles share a 32 KB instruction cache: an
+// unrolled variant that doubled the code ran at 82 % hit rate and 1.7x the time) and the hand-overs few.
 //
 // Replaces cuML's fusedL2NN + reduce_rows_by_key pair behind reference
 // python/src/spark_rapids_ml/clustering.py:367-370 (fit) and :493-497 (predict).
@@ -68,7 +75,6 @@ constexpr int kMaxKAcc = 32;  // passes with the update stage (register accumula
 #define B200KM_UPD_BATCH 4
 #endif
 constexpr int kUpdBatch = B200KM_UPD_BATCH;  // rows of a label's run loaded together by an update warp
-constexpr int kHist = 40;  // label bins (k + 1) rounded up
 
 // Per-row verdict written by the screen kernel: bits 0-7 the computed best centroid (the row's provisional
 // label, already counted in the sums), bits 8-15 the runner-up, bits 16-17 what the exact pass has to look at,
@@ -85,7 +91,10 @@ struct ScParams {
     int n_full;     // number of 32-float SWIZZLE_128B atoms
     int tail_cols;  // 0, 8 (SWIZZLE_32B) or 16 (SWIZZLE_64B): width of the narrow last atom
     int num_stages, num_d;
+    int stacked;  // 1: x^.c_hi and x^.c_lo land in separate TMEM column ranges (one MMA per K-step)
     int stage_bytes;
+    const float* X;
+    int prefetch;  // tiles the producer asks into L2 ahead of its loads (0 = none)
     const float* C;
     const float* cnorm;
     float* xnorm;  // [n] ||x||^2: written when xn_compute, read otherwise
@@ -120,16 +129,15 @@ __device__ __forceinline__ void mma_tf32_ss(uint32_t d_tmem, uint64_t a_desc, ui
         : "memory");
 }
 
-// acc (two packed floats) += v when pos < end.  One FADD2 for two columns; the predicate lives inside the
-// asm so the row loop stays branch-free.
-__device__ __forceinline__ void add2_if(unsigned long long& acc, unsigned long long v, int pos, int end) {
-    asm("{\n\t"
-        ".reg .pred p;\n\t"
-        "setp.lt.s32 p, %2, %3;\n\t"
-        "@p add.rn.f32x2 %0, %0, %1;\n\t"
-        "}"
-        : "+l"(acc)
-        : "l"(v), "r"(pos), "r"(end));
+// acc (two packed floats) += v * m, m = {1, 1} or {0, 0}: one FFMA2 for two columns, no branch and no select.
+// (v * 1 + acc rounds exactly like v + acc.)
+__device__ __forceinline__ void fma2(unsigned long long& acc, unsigned long long v, unsigned long long m) {
+    asm("fma.rn.f32x2 %0, %1, %2, %0;" : "+l"(acc) : "l"(v), "l"(m));
+}
+__device__ __forceinline__ unsigned long long pack2(float a, float b) {
+    unsigned long long r;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(a), "f"(b));
+    return r;
 }
 __device__ __forceinline__ float2 unpack2(unsigned long long v) {
     float2 r;
@@ -145,6 +153,36 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&r)[32]) {
           "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]),
           "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]),
           "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+        : "r"(taddr)
+        : "memory");
+}
+
+// The assign warps' waits: inline (a call would make the compiler wait for every load in flight first, and these
+// warps keep the next tile's row norms in flight across their waits).
+__device__ __forceinline__ void sc_wait(uint32_t bar, uint32_t parity) {
+    uint32_t ok;
+    do {
+        asm volatile(
+            "{\n\t"
+            ".reg .pred p;\n\t"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n\t"
+            "selp.u32 %0, 1, 0, p;\n\t"
+            "}"
+            : "=r"(ok)
+            : "r"(bar), "r"(parity), "r"(0x989680)
+            : "memory");
+    } while (!ok);
+}
+__device__ __forceinline__ float sqrt_up(float x) {  // >= sqrt(x): the approximate root (2 ulp) with slack
+    float r;
+    asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+    return r * 1.000001f;
+}
+__device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&r)[16]) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+          "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
         : "r"(taddr)
         : "memory");
 }
@@ -236,33 +274,42 @@ __device__ __forceinline__ void top3_of_32(const float (&key)[32], float& o1, fl
     o3 = m3[0];
 }
 
+// The exact decisions are made by groups of kSubW lanes (two rows per warp at a time: the loads of a row are
+// independent, and the phase is bound by the latency of HBM, not by arithmetic).  sub = lane within the group,
+// gmask = the group's lanes.
+#ifndef B200KM_FIX_SUBW
+#define B200KM_FIX_SUBW 16
+#endif
+constexpr int kSubW = B200KM_FIX_SUBW;
 __device__ __forceinline__ float sqdist_f32(const float4* __restrict__ x4, const float4* __restrict__ c4, int nchunks,
-                                            int lane) {
+                                            int sub, unsigned gmask) {
     float s = 0.f;
-    for (int ch = lane; ch < nchunks; ch += 32) {
+    for (int ch = sub; ch < nchunks; ch += kSubW) {
         const float4 xv = __ldg(x4 + ch), cv = __ldg(c4 + ch);
         const float d0 = xv.x - cv.x, d1 = xv.y - cv.y, d2 = xv.z - cv.z, d3 = xv.w - cv.w;
         s += fmaf(d0, d0, d1 * d1) + fmaf(d2, d2, d3 * d3);
     }
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+    for (int o = kSubW / 2; o > 0; o >>= 1) s += __shfl_xor_sync(gmask, s, o);
     return s;
 }
-__device__ __forceinline__ double sqdist_f64(const float* __restrict__ x, const float* __restrict__ c, int d, int lane) {
+__device__ __forceinline__ double sqdist_f64(const float* __restrict__ x, const float* __restrict__ c, int d, int sub,
+                                             unsigned gmask) {
     double s = 0.0;
-    for (int i = lane; i < d; i += 32) {
+    for (int i = sub; i < d; i += kSubW) {
         const double df = (double)__ldg(x + i) - (double)__ldg(c + i);
         s = fma(df, df, s);
     }
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+    for (int o = kSubW / 2; o > 0; o >>= 1) s += __shfl_xor_sync(gmask, s, o);
     return s;
 }
 
-// Exact label of one open row (one warp): FP32 squared differences, float64 when even those tie; ties keep the
-// lowest index.  word = the row's verdict (computed best, runner-up, which centroids to look at).
+// Exact label of one open row (one group of kSubW lanes): FP32 squared differences, float64 when even those tie; ties
+// keep the lowest index.  word = the row's verdict (computed best, runner-up, which centroids to look at).
 __device__ __forceinline__ int exact_label(const float* __restrict__ x, unsigned int word, int d, int k,
-                                           const float* __restrict__ C, const float* __restrict__ pd, int lane) {
+                                           const float* __restrict__ C, const float* __restrict__ pd, int sub,
+                                           unsigned gmask) {
     const int nchunks = d >> 2;
     const int i1 = (int)(word & 255u), i2 = (int)((word >> 8) & 255u);
     const unsigned int mode = word & (3u << 16);
@@ -270,12 +317,12 @@ __device__ __forceinline__ int exact_label(const float* __restrict__ x, unsigned
     int bi;
     if (mode == kInfoPair) {
         const int ja = min(i1, i2), jb = max(i1, i2);
-        const float sa = sqdist_f32(x4, reinterpret_cast<const float4*>(C + (size_t)ja * d), nchunks, lane);
-        const float sb = sqdist_f32(x4, reinterpret_cast<const float4*>(C + (size_t)jb * d), nchunks, lane);
+        const float sa = sqdist_f32(x4, reinterpret_cast<const float4*>(C + (size_t)ja * d), nchunks, sub, gmask);
+        const float sb = sqdist_f32(x4, reinterpret_cast<const float4*>(C + (size_t)jb * d), nchunks, sub, gmask);
         bi = sb < sa ? jb : ja;
         if (fabsf(sa - sb) <= 4e-6f * (sa + sb)) {
-            const double da = sqdist_f64(x, C + (size_t)ja * d, d, lane);
-            const double db = sqdist_f64(x, C + (size_t)jb * d, d, lane);
+            const double da = sqdist_f64(x, C + (size_t)ja * d, d, sub, gmask);
+            const double db = sqdist_f64(x, C + (size_t)jb * d, d, sub, gmask);
             bi = db < da ? jb : ja;
         }
         return bi;
@@ -283,12 +330,12 @@ __device__ __forceinline__ int exact_label(const float* __restrict__ x, unsigned
     // every centroid, or those that can beat the computed best c_1 at all: ||c_1 - c_j|| <= 2 ||x - c_1||
     float reach = FLT_MAX;
     if (mode == kInfoReach)
-        reach = 2.f * sqrtf(sqdist_f32(x4, reinterpret_cast<const float4*>(C + (size_t)i1 * d), nchunks, lane)) * 1.0001f;
+        reach = 2.f * sqrtf(sqdist_f32(x4, reinterpret_cast<const float4*>(C + (size_t)i1 * d), nchunks, sub, gmask)) * 1.0001f;
     float f1 = FLT_MAX, f2 = FLT_MAX;
     bi = i1;
     for (int j = 0; j < k; ++j) {
         if (j != i1 && reach < FLT_MAX && pd[(size_t)i1 * k + j] > reach) continue;
-        const float sum = sqdist_f32(x4, reinterpret_cast<const float4*>(C + (size_t)j * d), nchunks, lane);
+        const float sum = sqdist_f32(x4, reinterpret_cast<const float4*>(C + (size_t)j * d), nchunks, sub, gmask);
         if (sum < f1) {  // ascending index order: ties keep the lowest
             f2 = f1;
             f1 = sum;
@@ -301,7 +348,7 @@ __device__ __forceinline__ int exact_label(const float* __restrict__ x, unsigned
         double bd = DBL_MAX;
         for (int j = 0; j < k; ++j) {
             if (j != i1 && reach < FLT_MAX && pd[(size_t)i1 * k + j] > reach) continue;
-            const double sum = sqdist_f64(x, C + (size_t)j * d, d, lane);
+            const double sum = sqdist_f64(x, C + (size_t)j * d, d, sub, gmask);
             if (sum < bd) {
                 bd = sum;
                 bi = j;
@@ -363,14 +410,18 @@ __global__ void __launch_bounds__(256) screen_fixup_kernel(const float* __restri
             s_ent[off++] = (roff << 18) | (info[(size_t)chunk * kTileM + roff] & 0x3FFFFu);
         }
         __syncthreads();
-        // ---- exact labels: one warp per row ----
-        for (int i = warp; i < m; i += 8) {
-            const unsigned int e = s_ent[i];
-            const unsigned int roff = e >> 18;
-            const int bi = exact_label(Xc + (size_t)roff * d, e & 0x3FFFFu, d, k, C, pd, lane);
-            if (lane == 0) {
-                s_lab[i] = (unsigned char)bi;
-                if (labels && bi != (int)(e & 255u)) labels[(size_t)chunk * kTileM + roff] = bi;
+        // ---- exact labels: one group of kSubW lanes per row ----
+        {
+            const int sub = lane & (kSubW - 1);
+            const unsigned gmask = kSubW == 32 ? 0xffffffffu : ((1u << (kSubW & 31)) - 1u) << (lane & ~(kSubW - 1));
+            for (int i = tid / kSubW; i < m; i += 256 / kSubW) {
+                const unsigned int e = s_ent[i];
+                const unsigned int roff = e >> 18;
+                const int bi = exact_label(Xc + (size_t)roff * d, e & 0x3FFFFu, d, k, C, pd, sub, gmask);
+                if (sub == 0) {
+                    s_lab[i] = (unsigned char)bi;
+                    if (labels && bi != (int)(e & 255u)) labels[(size_t)chunk * kTileM + roff] = bi;
+                }
             }
         }
         __syncthreads();
@@ -454,11 +505,12 @@ __global__ void __launch_bounds__(kThreads, 1)
     if (p.honor_done && p.st->done) return;
 
     extern __shared__ uint8_t smem_raw[];
-    __shared__ uint8_t s_hist[2][2][4][kHist];         // per assign group, double-buffered by tile: per-warp label counts
-    __shared__ unsigned short s_base[2][kHist];        // start of every label's run in the sorted order (double-buffered)
-    __shared__ int s_perm[2][kTileM + 8];   // sorted position -> low 16 bits: row offset in a full atom
-                                            // (r*128 | swizzle); bit 16: first row of its run; bits 17+: label
-    __shared__ int s_permT[2][kTileM + 8];  // same for the narrow tail atom (row pitch 64 / 32 bytes)
+    // per assign group (= tile parity): bit r of s_mask[g][label][q] = row q*32 + r of the tile goes to `label`
+    __shared__ __align__(16) unsigned int s_mask[2][kMaxKAcc + 1][4];  // row kMaxKAcc stays zero (free slots)
+    // per update warp: its rows of the current tile, ordered by (owned label, row); low half = byte offset of the
+    // row inside a full atom (r*128 | swizzle), high half = the same inside the narrow tail atom
+    __shared__ unsigned int s_list[kOwnBinsLater][kTileM + 8];
+    __shared__ unsigned int s_cntw[8][32];  // per assign warp: decided rows per label (lane = label)
     __shared__ double s_sumxn[16];          // per assign warp: sum of ||x||^2 over its rows
     uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
     const uint32_t smem_base = smem_u32(smem);
@@ -472,8 +524,14 @@ __global__ void __launch_bounds__(kThreads, 1)
     // cycles on that path.
     const int stage_bytes = p.stage_bytes;
     const int c_block = 2 * p.k_pad * 128;  // bytes of one full-atom block [c_hi rows | c_lo rows]
-    const int dcols = p.k_pad;  // TMEM columns of one score buffer (the c_hi and c_lo products add up in place)
+    // TMEM columns of one score buffer.  stacked: one instruction per K-step against [c_hi ; c_lo] as 2*k_pad
+    // columns (the tile is read from shared memory once, the assign warps add the two halves); otherwise two
+    // instructions per K-step into the same k_pad columns.
+    const bool stacked = p.stacked != 0;
+    const int dcols = stacked ? 2 * p.k_pad : p.k_pad;
     const int n_groups = p.acc ? 2 : 4;  // assign groups: without an update stage its warps score tiles too
+    // update warps: 14-21, and - on passes that read the row norms back - the four idle norm warps as well
+    const int n_upd = p.xn_compute ? kOwnBinsFirst : kOwnBinsLater;
 
     // barrier table
     const uint32_t bar0 = smem_base + p.off_bar;
@@ -484,7 +542,7 @@ __global__ void __launch_bounds__(kThreads, 1)
     if (threadIdx.x == 0) {
         for (int s = 0; s < kMaxStages; ++s) {
             mbar_init(x_full0 + 8u * s, 1);
-            mbar_init(x_empty0 + 8u * s, p.acc ? 8 : 4);
+            mbar_init(x_empty0 + 8u * s, p.acc ? n_upd : 4);
             mbar_init(xn_full0 + 8u * s, 4);
         }
         for (int s = 0; s < kMaxND; ++s) {
@@ -493,7 +551,7 @@ __global__ void __launch_bounds__(kThreads, 1)
         }
         for (int s = 0; s < 2; ++s) {
             mbar_init(s_full0 + 8u * s, 4);
-            mbar_init(s_empty0 + 8u * s, 8);
+            mbar_init(s_empty0 + 8u * s, n_upd);
         }
         mbar_init(c_full, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -523,12 +581,10 @@ __global__ void __launch_bounds__(kThreads, 1)
         }
         if (threadIdx.x < 16) s_sumxn[threadIdx.x] = 0.0;
 #pragma unroll 1
-        for (int i = threadIdx.x; i < 2 * 2 * 4 * kHist; i += kThreads) (&s_hist[0][0][0][0])[i] = 0;
+        for (int i = threadIdx.x; i < 2 * (kMaxKAcc + 1) * 4; i += kThreads) (&s_mask[0][0][0])[i] = 0;
 #pragma unroll 1
-        for (int i = threadIdx.x; i < 2 * (kTileM + 8); i += kThreads) {
-            (&s_perm[0][0])[i] = 0;
-            (&s_permT[0][0])[i] = 0;
-        }
+        for (int i = threadIdx.x; i < kOwnBinsLater * (kTileM + 8); i += kThreads) (&s_list[0][0])[i] = 0;
+        if (threadIdx.x < 8 * 32) (&s_cntw[0][0])[threadIdx.x] = 0;
     }
     tc_fence_before();
     __syncthreads();
@@ -575,10 +631,21 @@ __global__ void __launch_bounds__(kThreads, 1)
                 for (int part = 0; part < 2; ++part)
                     tma_load_2d(smem_base + p.off_c + p.n_full * c_block + part * p.k_pad * p.tail_cols * 4, &tmCt,
                                 c_full, p.n_full * 32, part * p.k_pad);
+            // L2 runs ahead of the shared-memory stages: a tile is one contiguous range of X
+            const size_t tile_bytes = (size_t)kTileM * p.d * sizeof(float);
+            const size_t x_bytes = (size_t)p.n * p.d * sizeof(float);
+            auto prefetch_tile = [&](int64_t t) {
+                if (t >= p.num_tiles) return;
+                const size_t off = (size_t)t * tile_bytes;
+                const size_t len = x_bytes - off < tile_bytes ? x_bytes - off : tile_bytes;
+                prefetch_l2_bulk(reinterpret_cast<const char*>(p.X) + off, (uint32_t)len);
+            };
+            for (int a = 1; a < p.prefetch; ++a) prefetch_tile(first_tile + (int64_t)a * tile_step);
             int64_t it = 0;
             int s = 0;
             uint32_t sph = 0;  // phase of stage s
             for (int64_t tile = first_tile; tile < p.num_tiles; tile += tile_step, ++it) {
+                if (p.prefetch) prefetch_tile(tile + (int64_t)p.prefetch * tile_step);
                 mbar_wait(x_empty0 + 8u * s, sph ^ 1u);
                 trace_ev(p, it, 0);
                 mbar_arrive_expect_tx(x_full0 + 8u * s, (uint32_t)stage_bytes);
@@ -627,20 +694,33 @@ __global__ void __launch_bounds__(kThreads, 1)
             const uint64_t soff = (uint64_t)((s * stage_bytes) >> 4);
             if (elect_one()) {
                 uint64_t ad = adesc_full + soff, bd = bdesc_full;
+                if (stacked) {
 #pragma unroll 1
-                for (int a = 0; a < p.n_full; ++a) {
+                    for (int a = 0; a < p.n_full; ++a) {
 #pragma unroll
-                    for (int kk = 0; kk < 4; ++kk) {
-                        mma_tf32_ss(d_tmem, ad + 2 * kk, bd + 2 * kk, idesc, (a | kk) != 0);
-                        mma_tf32_ss(d_tmem, ad + 2 * kk, bd + lo_full + 2 * kk, idesc, 1);
+                        for (int kk = 0; kk < 4; ++kk) mma_tf32_ss(d_tmem, ad + 2 * kk, bd + 2 * kk, idesc, (a | kk) != 0);
+                        ad += (uint64_t)(kAtomBytes >> 4);
+                        bd += (uint64_t)(c_block >> 4);
                     }
-                    ad += (uint64_t)(kAtomBytes >> 4);
-                    bd += (uint64_t)(c_block >> 4);
-                }
 #pragma unroll 1
-                for (int kk = 0; kk < tail_steps; ++kk) {
-                    mma_tf32_ss(d_tmem, adesc_tail + soff + 2 * kk, bdesc_tail + 2 * kk, idesc, (p.n_full | kk) != 0);
-                    mma_tf32_ss(d_tmem, adesc_tail + soff + 2 * kk, bdesc_tail + lo_tail + 2 * kk, idesc, 1);
+                    for (int kk = 0; kk < tail_steps; ++kk)
+                        mma_tf32_ss(d_tmem, adesc_tail + soff + 2 * kk, bdesc_tail + 2 * kk, idesc, (p.n_full | kk) != 0);
+                } else {
+#pragma unroll 1
+                    for (int a = 0; a < p.n_full; ++a) {
+#pragma unroll
+                        for (int kk = 0; kk < 4; ++kk) {
+                            mma_tf32_ss(d_tmem, ad + 2 * kk, bd + 2 * kk, idesc, (a | kk) != 0);
+                            mma_tf32_ss(d_tmem, ad + 2 * kk, bd + lo_full + 2 * kk, idesc, 1);
+                        }
+                        ad += (uint64_t)(kAtomBytes >> 4);
+                        bd += (uint64_t)(c_block >> 4);
+                    }
+#pragma unroll 1
+                    for (int kk = 0; kk < tail_steps; ++kk) {
+                        mma_tf32_ss(d_tmem, adesc_tail + soff + 2 * kk, bdesc_tail + 2 * kk, idesc, (p.n_full | kk) != 0);
+                        mma_tf32_ss(d_tmem, adesc_tail + soff + 2 * kk, bdesc_tail + lo_tail + 2 * kk, idesc, 1);
+                    }
                 }
                 tc_commit(d_full0 + 8u * db);
                 trace_ev(p, it, 2);
@@ -651,9 +731,9 @@ __global__ void __launch_bounds__(kThreads, 1)
                 sph ^= 1u;
             }
         }
-    } else if (warp >= kNormWarp0 && warp < kAssignWarp0) {
+    } else if (warp >= kNormWarp0 && warp < kAssignWarp0 && p.xn_compute) {
         // ======================================= row norms ======================================
-        if (p.xn_compute) {
+        {
             const int row = (warp - kNormWarp0) * 32 + lane;
             float* xn_s = (float*)(smem + p.off_xn);
             int s = 0;
@@ -685,7 +765,6 @@ __global__ void __launch_bounds__(kThreads, 1)
         const int q = warp & 3;  // = the warp's TMEM lane quarter
         const int row = q * 32 + lane;
         const int et = threadIdx.x - (kAssignWarp0 + 4 * g) * 32;  // 0..127 within the group
-        const int bar_id = 1 + g;
         float* cn_s = (float*)(smem + p.off_cn);
         float* xn_s = (float*)(smem + p.off_xn);
         const float cmax = p.st->cnorm_max;
@@ -694,20 +773,31 @@ __global__ void __launch_bounds__(kThreads, 1)
         const int sb = g;
 
         double sum_xn = 0.0;
+        unsigned int cnt_lane = 0u;  // lane = label: rows this warp has decided for it
         int s = g % S;
         uint32_t sph = (uint32_t)((g / S) & 1);  // g < 4: cheap, once
         int64_t tile = first_tile + (int64_t)g * tile_step;
         const int64_t group_step = (int64_t)n_groups * tile_step;
+        // the row norms of a pass that reads them back are fetched one tile ahead (HBM latency under load is
+        // longer than a tile's turn)
+        float xn_next = 0.f, xl_next = 0.f;
+        if (!p.xn_compute && tile < p.num_tiles && tile * kTileM + row < p.n) {
+            xn_next = p.xnorm[tile * kTileM + row];
+            xl_next = p.xlo[tile * kTileM + row];
+        }
         for (int64_t it = g; tile < p.num_tiles; it += n_groups, tile += group_step) {
             const int db = (int)(it & (ND - 1));
             const int64_t grow = tile * kTileM + row;
             const bool valid = grow < p.n;
-            float xn = 0.f, xl = 0.f;
-            if (!p.xn_compute && valid) {  // issued early, consumed after the scores
-                xn = p.xnorm[grow];
-                xl = p.xlo[grow];
+            float xn = xn_next, xl = xl_next;
+            {
+                const int64_t grow_next = grow + group_step * kTileM;
+                if (!p.xn_compute && grow_next < p.n) {
+                    xn_next = p.xnorm[grow_next];
+                    xl_next = p.xlo[grow_next];
+                }
             }
-            mbar_wait(d_full0 + 8u * db, (uint32_t)((it / ND) & 1));
+            sc_wait(d_full0 + 8u * db, (uint32_t)((it / ND) & 1));
             tc_fence_after();
             if (et == 0) trace_ev(p, it, 4);
 
@@ -717,7 +807,7 @@ __global__ void __launch_bounds__(kThreads, 1)
             // ---- 32 scores at a time into registers; keys D_j = ||x||^2 + ||c_j||^2 - 2 x^.c_j carry the centroid
             // index in their 7 low mantissa bits (a perturbation below 2^-16 |D_j|, covered by the bound) ----
             if (p.xn_compute) {
-                mbar_wait(xn_full0 + 8u * s, sph);
+                sc_wait(xn_full0 + 8u * s, sph);
                 xn = xn_s[s * kTileM + row];
                 xl = xn_s[(kMaxStages + s) * kTileM + row];
             }
@@ -725,8 +815,21 @@ __global__ void __launch_bounds__(kThreads, 1)
 #pragma unroll 1
             for (int c0 = 0; c0 < p.k_pad; c0 += 32) {
                 uint32_t sc[32];
-                tmem_ld32(taddr + c0, sc);
-                tmem_wait_ld();
+                if (stacked) {  // x^.c_hi + x^.c_lo: the two column ranges, 16 columns at a time
+#pragma unroll
+                    for (int hh = 0; hh < 2; ++hh) {
+                        uint32_t sh[16], sl[16];
+                        tmem_ld16(taddr + c0 + 16 * hh, sh);
+                        tmem_ld16(taddr + p.k_pad + c0 + 16 * hh, sl);
+                        tmem_wait_ld();
+#pragma unroll
+                        for (int j = 0; j < 16; ++j)
+                            sc[16 * hh + j] = __float_as_uint(__uint_as_float(sh[j]) + __uint_as_float(sl[j]));
+                    }
+                } else {
+                    tmem_ld32(taddr + c0, sc);
+                    tmem_wait_ld();
+                }
                 float key[32];
                 const float4* cn4 = reinterpret_cast<const float4*>(cn_s + c0);
 #pragma unroll
@@ -757,9 +860,9 @@ __global__ void __launch_bounds__(kThreads, 1)
             label = i1;
             // safety test (see the file header); every quantity is an upper bound
             const float scale = xn + cmax;
-            const float t = p.tol_x * sqrtf(xl);  // >= ||x - x^||
+            const float t = p.tol_x * sqrt_up(xl);  // >= ||x - x^||
             const float eps = p.eps_rel * scale + 1.6e-5f * (fabsf(b1) + fabsf(b2));
-            const float r1 = sqrtf(fmaxf(b1, 0.f) + p.abs_rel * scale);
+            const float r1 = sqrt_up(fmaxf(b1, 0.f) + p.abs_rel * scale);
             const float safe = 4.f * t * r1 + eps;
             const float margin = b2 - b1;
             // runner-up: the pair bound.  Any other centroid j can truly beat c_1 only if ||c_1 - c_j|| <= 2 r_1:
@@ -788,50 +891,19 @@ __global__ void __launch_bounds__(kThreads, 1)
             if (et == 0) trace_ev(p, it, 5);
 
             if (p.acc) {
-                // ---- stable counting sort of the tile's rows by label (bin k = rows past the end) ----
-                // One barrier: every warp publishes its label counts, then each warp derives its own start
-                // offsets from all four count rows by itself (a scan over the bins), so there is no serial
-                // section.  The count rows are double-buffered by tile; a warp clears its row of the other
-                // buffer after the barrier (everyone is then done reading that buffer's previous use).
-                mbar_wait(s_empty0 + 8u * sb, (uint32_t)(((it >> 1) & 1) ^ 1));
-                const int hb = (int)((it >> 1) & 1);
-                uint8_t (*hist)[kHist] = s_hist[g][hb];
-                // Rows that are open (the exact pass adds them) or past the end take no part: bin -1.
-                const int bins = p.k;
+                // ---- which rows go to which label: one mask word per (label, warp) ----
+                // Rows that are open (the exact pass adds them) or past the end take no part.  The update warps
+                // turn the masks of the labels they own into row lists themselves: no barrier among the assign
+                // warps, no sorted permutation to hand over.
+                sc_wait(s_empty0 + 8u * sb, (uint32_t)(((it >> 1) & 1) ^ 1));
                 const int bin = (valid && !amb) ? label : -1;
-                const unsigned peers = __match_any_sync(0xffffffffu, bin);
-                const int rank_w = __popc(peers & ((1u << lane) - 1u));
-                if (bin >= 0 && rank_w == 0) hist[q][bin] = (uint8_t)__popc(peers);
-                named_bar_sync(bar_id, 128);
-                int pos, first;
-                // lane = bin
-                const int h0 = hist[0][lane], h1 = hist[1][lane], h2 = hist[2][lane], h3 = hist[3][lane];
-                const int tot = (lane < bins) ? h0 + h1 + h2 + h3 : 0;
-                int incl = tot;
-#pragma unroll
-                for (int o = 1; o < 32; o <<= 1) {
-                    const int v = __shfl_up_sync(0xffffffffu, incl, o);
-                    if (lane >= o) incl += v;
-                }
-                const int excl = incl - tot;
-                const int mine = excl + (q > 0 ? h0 : 0) + (q > 1 ? h1 : 0) + (q > 2 ? h2 : 0);
-                if (q == 0) s_base[sb][lane] = (unsigned short)excl;  // lanes >= bins hold the number of placed rows
-                if (q == 0 && lane == 31) s_base[sb][32] = (unsigned short)incl;
-                pos = __shfl_sync(0xffffffffu, mine, bin & 31) + rank_w;
-                first = pos == __shfl_sync(0xffffffffu, excl, bin & 31);
-                if (bin >= 0) {
-                    // sorted position -> row offset inside an atom (r*pitch | swizzle bits), a first-of-run flag
-                    // (bit 16) and the label (bits 17+)
-                    const int meta = (first ? (1 << 16) : 0) | (bin << 17);
-                    s_perm[sb][pos] = (row << 7) | ((row & 7) << 4) | meta;
-                    if (p.tail_cols == 16) s_permT[sb][pos] = (row << 6) | (((row >> 1) & 3) << 4) | meta;
-                    else if (p.tail_cols == 8) s_permT[sb][pos] = (row << 5) | (((row >> 2) & 1) << 4) | meta;
-                }
-                {
-                    uint8_t* nxt = s_hist[g][hb ^ 1][q];
-                    for (int bb = lane; bb < bins; bb += 32) nxt[bb] = 0;  // own row of the other buffer
-                }
-                __syncwarp();  // the warp's s_perm writes precede its arrival; the update group waits for all four
+                // every row ORs its bit into its label's word (order does not matter for an OR)
+                if (lane < p.k) s_mask[sb][lane][q] = 0u;
+                __syncwarp();
+                if (bin >= 0) atomicOr(&s_mask[sb][bin][q], 1u << lane);
+                __syncwarp();
+                if (lane < p.k) cnt_lane += (unsigned int)__popc(s_mask[sb][lane][q]);
+                __syncwarp();  // the warp's mask words precede its arrival; the update warps wait for all four
                 if (et == 0) trace_ev(p, it, 6);
                 if (lane == 0) mbar_arrive(s_full0 + 8u * sb);
             } else {
@@ -849,21 +921,28 @@ __global__ void __launch_bounds__(kThreads, 1)
             sum_xn += __shfl_xor_sync(0xffffffffu, sum_xn, o);
         }
         if (lane == 0 && p.acc) s_sumxn[warp - kAssignWarp0] = sum_xn;
-    } else if (warp >= kUpdateWarp0 && p.acc) {
+        if (p.acc) s_cntw[warp - kAssignWarp0][lane] = cnt_lane;
+    } else if (p.acc && (warp >= kUpdateWarp0 || warp < kAssignWarp0)) {
         // ======================================== update ========================================
-        // Eight warps; warp u owns the labels [u*k/8, (u+1)*k/8) for the whole kernel, i.e. one contiguous
-        // range of each tile's label-sorted rows; lane = float4 column chunk.  No other thread ever touches
-        // an owner's (label, column) sums, so no atomics are needed anywhere in the tile loop.
-        const int u = warp - kUpdateWarp0;
-        const int ut = threadIdx.x - kUpdateWarp0 * 32;
+        // Eight warps; warp u owns the labels IterState::own[u*4..] (<= 4, balanced by cluster size after every
+        // iteration) for the whole kernel; lane = float4 column chunk.  Their FP32 sums live in registers (two packed
+        // pairs per label, FADD2) and are folded into the CTA's float64 shared accumulators every 8 tiles.  No other
+        // thread touches an owner's sums: no atomics.  The code is kept small on purpose: the roles of this kernel
+        // share a 32 KB instruction cache, and a miss costs an L2 round trip.
+        const int u = warp >= kUpdateWarp0 ? warp - kUpdateWarp0 : 8 + warp - kNormWarp0;
+        const int ut = u * 32 + lane;
         double* sacc = (double*)(smem + p.off_acc);
         const int nchunks = p.d >> 2;
-        // k <= 32: at most 4 owned labels.  Their FP32 sums live in registers (two packed pairs per
-        // label, added with FADD2) and are folded into the float64 shared accumulators every 8 tiles.
-        // Rows come in batches of 8 with predicated adds: a lone warp pays ~20 cycles per taken branch.
-        int lab[4];  // owned labels (-1 = free slot): balanced by cluster size, see IterState::own
+        int lab[4];  // owned labels; kMaxKAcc = free slot (its mask row is all zero)
+        {
+            const bool table = p.st->own_bins == n_upd;  // else (never on b200km_fit's schedule): contiguous ranges
+            const int lo = (u * p.k) / n_upd, hi = ((u + 1) * p.k) / n_upd;
 #pragma unroll
-        for (int li = 0; li < 4; ++li) lab[li] = p.st->own[u * 4 + li];
+            for (int li = 0; li < 4; ++li) {
+                const int l = table ? (int)p.st->own[u * 4 + li] : (lo + li < hi ? lo + li : -1);
+                lab[li] = l < 0 ? kMaxKAcc : l;
+            }
+        }
         const bool active = lane < nchunks;
         const int ch = active ? lane : 0;
         const int a = ch >> 3;
@@ -871,70 +950,92 @@ __global__ void __launch_bounds__(kThreads, 1)
         const int col_off = (tail ? p.n_full : a) * kAtomBytes;
         const int c16 = (tail ? (ch - p.n_full * 8) : (ch & 7)) << 4;
         unsigned long long acc[4][2];
-        int cnt[4];
 #pragma unroll
-        for (int li = 0; li < 4; ++li) {
-            acc[li][0] = acc[li][1] = 0ull;
-            cnt[li] = 0;
-        }
+        for (int li = 0; li < 4; ++li) acc[li][0] = acc[li][1] = 0ull;
         auto fold = [&]() {
 #pragma unroll
             for (int li = 0; li < 4; ++li) {
-                if (lab[li] >= 0) {
-                    if (active) {
-                        double2* dst = reinterpret_cast<double2*>(sacc + (size_t)lab[li] * p.d + ch * 4);
-                        const float2 lo = unpack2(acc[li][0]), hi = unpack2(acc[li][1]);
-                        double2 a0 = dst[0], a1 = dst[1];
-                        a0.x += (double)lo.x;
-                        a0.y += (double)lo.y;
-                        a1.x += (double)hi.x;
-                        a1.y += (double)hi.y;
-                        dst[0] = a0;
-                        dst[1] = a1;
-                    }
-                    if (lane == 0) sacc[p.k * p.d + lab[li]] += (double)cnt[li];
-                    acc[li][0] = acc[li][1] = 0ull;
-                    cnt[li] = 0;
+                if (lab[li] < kMaxKAcc && active) {
+                    double2* dst = reinterpret_cast<double2*>(sacc + (size_t)lab[li] * p.d + ch * 4);
+                    const float2 lo = unpack2(acc[li][0]), hi = unpack2(acc[li][1]);
+                    double2 a0 = dst[0], a1 = dst[1];
+                    a0.x += (double)lo.x;
+                    a0.y += (double)lo.y;
+                    a1.x += (double)hi.x;
+                    a1.y += (double)hi.y;
+                    dst[0] = a0;
+                    dst[1] = a1;
                 }
+                acc[li][0] = acc[li][1] = 0ull;
             }
         };
+        // this lane's rows lane, 32 + lane, ... as list entries (offset in a full atom | offset in the tail atom << 16)
+        unsigned int enc[4];
+#pragma unroll
+        for (int w = 0; w < 4; ++w) {
+            const int r = w * 32 + lane;
+            const unsigned int full = (unsigned int)((r << 7) | ((r & 7) << 4));
+            const unsigned int tl = p.tail_cols == 16 ? (unsigned int)((r << 6) | (((r >> 1) & 3) << 4))
+                                                      : (unsigned int)((r << 5) | (((r >> 2) & 1) << 4));
+            enc[w] = full | (tl << 16);
+        }
+        const unsigned int lt = (1u << lane) - 1u;
+        unsigned int* list = s_list[u];
+        // the half of a list entry this lane's column chunk needs
+        const unsigned short* perm = reinterpret_cast<const unsigned short*>(list) + (tail ? 1 : 0);
         int64_t it = 0;
         int s = 0;
         uint32_t sph = 0;
         for (int64_t tile = first_tile; tile < p.num_tiles; tile += tile_step, ++it) {
             const int sb = (int)(it & 1);
             mbar_wait(s_full0 + 8u * sb, (uint32_t)((it >> 1) & 1));
-            mbar_wait(x_full0 + 8u * s, sph);
             if (ut == 0) trace_ev(p, it, 7);
-            const uint8_t* colp = smem + (size_t)s * stage_bytes + col_off;
-            // low halves of the perm words = byte offsets inside the atom
-            const unsigned short* perm = reinterpret_cast<const unsigned short*>(tail ? s_permT[sb] : s_perm[sb]);
+            // ---- the rows of the owned labels, label by label in ascending row order (= a stable sort) ----
+            int rb[5];
+            rb[0] = 0;
 #pragma unroll
             for (int li = 0; li < 4; ++li) {
-                if (lab[li] >= 0) {
-                    const int beg = s_base[sb][lab[li]], end = s_base[sb][lab[li] + 1];
+                if (lab[li] == kMaxKAcc) {  // free slot (uniform)
+                    rb[li + 1] = rb[li];
+                    continue;
+                }
+                const uint4 m = *reinterpret_cast<const uint4*>(&s_mask[sb][lab[li]][0]);
+                const int c0 = __popc(m.x), c1 = __popc(m.y), c2 = __popc(m.z), c3 = __popc(m.w);
+                const int b0 = rb[li];
+                if ((m.x >> lane) & 1u) list[b0 + __popc(m.x & lt)] = enc[0];
+                if ((m.y >> lane) & 1u) list[b0 + c0 + __popc(m.y & lt)] = enc[1];
+                if ((m.z >> lane) & 1u) list[b0 + c0 + c1 + __popc(m.z & lt)] = enc[2];
+                if ((m.w >> lane) & 1u) list[b0 + c0 + c1 + c2 + __popc(m.w & lt)] = enc[3];
+                rb[li + 1] = b0 + c0 + c1 + c2 + c3;
+            }
+            __syncwarp();
+            if (lane == 0) mbar_arrive(s_empty0 + 8u * sb);  // the masks are consumed: the assign group may go on
+            if (ut == 0) trace_ev(p, it, 3);
+            mbar_wait(x_full0 + 8u * s, sph);
+            const uint8_t* colp = smem + (size_t)s * stage_bytes + col_off;
+#pragma unroll
+            for (int li = 0; li < 4; ++li) {
+                const int end = rb[li + 1];
 #pragma unroll 1
-                    for (int base = beg; base < end; base += kUpdBatch) {
-                        unsigned int w[kUpdBatch];
-                        ulonglong2 v[kUpdBatch];
+                for (int base = rb[li]; base < end; base += kUpdBatch) {
+                    unsigned int w[kUpdBatch];
+                    ulonglong2 v[kUpdBatch];
+                    // rows past the end repeat the last one with weight 0 (always a row of this label)
 #pragma unroll
-                        for (int j = 0; j < kUpdBatch; ++j) w[j] = perm[2 * (base + j)];  // past `end`: stale but valid offsets
+                    for (int j = 0; j < kUpdBatch; ++j) w[j] = perm[2 * min(base + j, end - 1)];
 #pragma unroll
-                        for (int j = 0; j < kUpdBatch; ++j) v[j] = *reinterpret_cast<const ulonglong2*>(colp + (w[j] ^ c16));
+                    for (int j = 0; j < kUpdBatch; ++j) v[j] = *reinterpret_cast<const ulonglong2*>(colp + (w[j] ^ c16));
 #pragma unroll
-                        for (int j = 0; j < kUpdBatch; ++j) {
-                            add2_if(acc[li][0], v[j].x, base + j, end);
-                            add2_if(acc[li][1], v[j].y, base + j, end);
-                        }
+                    for (int j = 0; j < kUpdBatch; ++j) {
+                        const float on = base + j < end ? 1.f : 0.f;
+                        const unsigned long long m = pack2(on, on);
+                        fma2(acc[li][0], v[j].x, m);
+                        fma2(acc[li][1], v[j].y, m);
                     }
-                    cnt[li] += end - beg;
                 }
             }
             __syncwarp();
-            if (lane == 0) {
-                mbar_arrive(s_empty0 + 8u * sb);
-                mbar_arrive(x_empty0 + 8u * s);
-            }
+            if (lane == 0) mbar_arrive(x_empty0 + 8u * s);
             if (lane == 0) trace_ev(p, it, 8 + u);
             if ((it & 7) == 7 || tile + tile_step >= p.num_tiles) fold();  // single (rare) fold site
             if (++s == S) {
@@ -961,7 +1062,12 @@ __global__ void __launch_bounds__(kThreads, 1)
         const double* sacc = (const double*)(smem + p.off_acc);
         const int acc_n = p.k * p.d + p.k;
 #pragma unroll 1
-        for (int i = threadIdx.x; i < acc_n; i += kThreads) slot[i] = sacc[i];
+        for (int i = threadIdx.x; i < p.k * p.d; i += kThreads) slot[i] = sacc[i];
+        if (threadIdx.x < p.k) {
+            unsigned int c = 0;
+            for (int w = 0; w < 8; ++w) c += s_cntw[w][threadIdx.x];
+            slot[p.k * p.d + threadIdx.x] = (double)c;
+        }
         if (threadIdx.x == 0) {
             double t = 0.0;
             for (int w = 0; w < 16; ++w) t += s_sumxn[w];
@@ -974,7 +1080,7 @@ __global__ void __launch_bounds__(kThreads, 1)
 }
 
 // ---- host side ---------------------------------------------------------------------------------
-constexpr int kStaticSmem = 4 * 1024;  // upper bound of the kernel's static shared arrays
+constexpr int kStaticSmem = 9 * 1024;  // upper bound of the kernel's static shared arrays
 
 struct Plan {
     int k_pad, n_full, tail_cols, d_pad, num_stages, num_d, stage_bytes;
@@ -1038,6 +1144,37 @@ size_t screen_workspace_bytes(int d, int k) {
     return pl.ok ? sizeof(float) * (2 * (size_t)pl.k_pad * pl.d_pad + (size_t)k * k) : 0;
 }
 const char* screen_last_error() { return g_sc_err; }
+
+#ifdef B200KM_ENABLE_TRACE
+namespace {
+struct KTime {  // development builds: B200KM_KTIME=1 prints the mean time of the pass's kernels at exit
+    cudaEvent_t ev[64][4];
+    int n = 0;
+    bool on = getenv("B200KM_KTIME") != nullptr;
+    ~KTime() {
+        if (!on || n < 4) return;
+        double t[3] = {0, 0, 0};
+        int m = 0;
+        for (int i = n / 2; i < n; ++i, ++m)
+            for (int j = 0; j < 3; ++j) {
+                float ms = 0;
+                cudaEventElapsedTime(&ms, ev[i][j], ev[i][j + 1]);
+                t[j] += ms;
+            }
+        fprintf(stderr, "KTIME over %d passes: prep %.4f  screen %.4f  fixup+reduce %.4f ms\n", m, t[0] / m, t[1] / m, t[2] / m);
+    }
+    void mark(int j, cudaStream_t s) {
+        if (!on || n >= 64) return;
+        if (j == 0) for (int q = 0; q < 4; ++q) cudaEventCreate(&ev[n][q]);
+        cudaEventRecord(ev[n][j], s);
+        if (j == 3) ++n;
+    }
+} g_ktime;
+}
+#define KT(j) g_ktime.mark(j, s)
+#else
+#define KT(j)
+#endif
 
 int screen_pass(TcWorkspace* ws, const float* X, int64_t n, int d, int k, const float* C, const float* cnorm,
                 float* xnorm, float* xlo, unsigned int* info, bool xn_compute, int32_t* labels, double* acc,
@@ -1132,6 +1269,7 @@ int screen_pass(TcWorkspace* ws, const float* X, int64_t n, int d, int k, const 
     {
         int split_blocks = (pl.k_pad * pl.d_pad + 127) / 128;
         if (split_blocks > kNumSMs) split_blocks = kNumSMs;
+        KT(0);
         screen_prep_kernel<<<split_blocks + (k * k + 3) / 4, 128, 0, s>>>(C, k, d, pl.k_pad, pl.d_pad, split_blocks,
                                                                          (float*)ws->d_buf, (float*)ws->d_pd);
         count_launch();
@@ -1146,7 +1284,13 @@ int screen_pass(TcWorkspace* ws, const float* X, int64_t n, int d, int k, const 
     p.tail_cols = pl.tail_cols;
     p.num_stages = pl.num_stages;
     p.num_d = pl.num_d;
+    p.stacked = (2 * pl.k_pad * kMaxND <= 512) ? 1 : 0;
     p.stage_bytes = pl.stage_bytes;
+    p.X = X;
+    p.prefetch = 3;
+#ifdef B200KM_ENABLE_TRACE
+    if (const char* e = getenv("B200KM_PREFETCH")) p.prefetch = atoi(e);
+#endif
     p.C = C;
     p.cnorm = cnorm;
     p.xnorm = xnorm;
@@ -1168,7 +1312,7 @@ int screen_pass(TcWorkspace* ws, const float* X, int64_t n, int d, int k, const 
     // eps_rel * (||x||^2 + max||c||^2) of it; one D_j alone is off by at most abs_rel * (same scale).
     p.pd = (const float*)ws->d_pd;
     p.tol_x = 1.002f;
-    p.eps_rel = 2.f * (float)((d + 7) / 8 + 6) * 1.1920928955078125e-07f + 1e-6f;
+    p.eps_rel = 2.f * (float)((d + 7) / 8 + 7) * 1.1920928955078125e-07f + 1e-6f;
     p.abs_rel = 9.765625e-4f * 1.001f + p.eps_rel;
     p.off_c = pl.off_c;
     p.off_acc = pl.off_acc;
@@ -1179,6 +1323,7 @@ int screen_pass(TcWorkspace* ws, const float* X, int64_t n, int d, int k, const 
     p.trace = nullptr;
 #ifdef B200KM_ENABLE_TRACE  // development builds only (B200KM_ENABLE_TRACE=1 python -m ...build)
     const char* trace_path = getenv("B200KM_TRACE");
+    if (getenv("B200KM_NO_STACK")) p.stacked = 0;
     if (trace_path && acc) {
         cudaMalloc((void**)&p.trace, 4096 * sizeof(unsigned long long));
         cudaMemsetAsync(p.trace, 0, 4096 * sizeof(unsigned long long), s);
@@ -1186,7 +1331,9 @@ int screen_pass(TcWorkspace* ws, const float* X, int64_t n, int d, int k, const 
 #endif
     int64_t grid = p.num_tiles < kNumSMs ? p.num_tiles : kNumSMs;
     if (grid < 1) grid = 1;
+    KT(1);
     kmeans_screen_kernel<<<(unsigned)grid, kThreads, pl.total, s>>>(tmX, tmXt, tmC, tmCt, p);
+    KT(2);
     count_launch();
     cudaError_t err = cudaGetLastError();
     if (err != cudaSuccess) {
@@ -1207,6 +1354,7 @@ int screen_pass(TcWorkspace* ws, const float* X, int64_t n, int d, int k, const 
             count_launch();
         }
     }
+    KT(3);
 #ifdef B200KM_ENABLE_TRACE
     if (p.trace) {  // development aid: synchronous dump of CTA 0's per-tile event clocks
         static unsigned long long host[256 * 16];

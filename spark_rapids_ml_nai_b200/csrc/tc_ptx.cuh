@@ -37,6 +37,28 @@ static __device__ __noinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
         "r"(parity), "r"(0x989680)
         : "memory");
 }
+// Asks for [gptr, gptr + bytes) to be brought into L2 (no destination, no completion to wait for): the later TMA
+// load of the same bytes into shared memory then pays the L2 latency instead of the HBM latency under load, so a
+// shared-memory stage is occupied for a shorter time per tile.  gptr 16-byte aligned, bytes a multiple of 16.
+__device__ __forceinline__ void prefetch_l2_bulk(const void* gptr, uint32_t bytes) {
+    asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(gptr), "r"(bytes) : "memory");
+}
+// The same wait without a call: a call makes the compiler wait for every load in flight first, so a role that
+// keeps global loads in flight across its waits (prefetched row norms) uses this one.
+__device__ __forceinline__ void mbar_wait_spin(uint32_t bar, uint32_t parity) {
+    uint32_t ok;
+    do {
+        asm volatile(
+            "{\n\t"
+            ".reg .pred p;\n\t"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n\t"
+            "selp.u32 %0, 1, 0, p;\n\t"
+            "}"
+            : "=r"(ok)
+            : "r"(bar), "r"(parity), "r"(0x989680)
+            : "memory");
+    } while (!ok);
+}
 __device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* tm, uint32_t bar, int c0, int c1) {
     asm volatile(
         "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];" ::"r"(dst),

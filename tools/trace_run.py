@@ -3,12 +3,15 @@ import sys, os
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
 from spark_rapids_ml_nai_b200 import _native
-n, d, k = 4_000_000, 100, 20
+n, d, k = int(os.environ.get('TRACE_ROWS', 4_000_000)), 100, 20
 dev = torch.device("cuda:0")
 g = torch.Generator(device=dev); g.manual_seed(1)
 centers = torch.rand((k, d), generator=g, device=dev) * 20.0 - 10.0
-lab = torch.randint(0, k, (n,), generator=g, device=dev)
-X = torch.randn((n, d), generator=g, device=dev) + centers[lab]
+X = torch.empty((n, d), dtype=torch.float32, device=dev)
+for s0 in range(0, n, 1 << 20):
+    e0 = min(n, s0 + (1 << 20))
+    lab = torch.randint(0, k, (e0 - s0,), generator=g, device=dev)
+    X[s0:e0] = torch.randn((e0 - s0, d), generator=g, device=dev) + centers[lab]
 h = _native.Handle(0)
 h.set_path(int(sys.argv[1]) if len(sys.argv) > 1 else _native.PATH_TC)
 C = centers.contiguous() if len(sys.argv) < 3 else X[torch.randperm(n, generator=g, device=dev)[:k]].clone()
