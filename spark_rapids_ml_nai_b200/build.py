@@ -7,7 +7,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIBDIR = os.path.join(HERE, "lib")
 LIB = os.path.join(LIBDIR, "libb200km.so")
-SOURCES = ["api.cu", "kernels_generic.cu", "kernels_tc.cu", "kernels_screen.cu", "kernels_gemm.cu", "kernels_update.cu", "kernels_init.cu", "kernels_small.cu", "noalloc.cu"]
+SOURCES = ["api.cu", "kernels_generic.cu", "kernels_tc.cu", "kernels_screen.cu", "kernels_fixup.cu", "kernels_gemm.cu", "kernels_update.cu", "kernels_init.cu", "kernels_small.cu", "noalloc.cu"]
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
     "-Xcompiler", "-fPIC,-O2,-Wall", "--expt-relaxed-constexpr",

@@ -61,7 +61,6 @@ using namespace tcx;
 
 thread_local char g_sc_err[512] = "";
 
-constexpr int kTileM = 128;
 constexpr int kAtomBytes = kTileM * 128;  // one full K-atom of an X tile: 128 rows x 32 floats
 constexpr int kThreads = 704;
 constexpr int kNormWarp0 = 2, kAssignWarp0 = 6, kUpdateWarp0 = 14;
@@ -76,14 +75,6 @@ constexpr int kMaxKAcc = 32;  // passes with the update stage (register accumula
 #endif
 constexpr int kUpdBatch = B200KM_UPD_BATCH;  // rows of a label's run loaded together by an update warp
 
-// Per-row verdict written by the screen kernel: bits 0-7 the computed best centroid (the row's provisional
-// label, already counted in the sums), bits 8-15 the runner-up, bits 16-17 what the exact pass has to look at,
-// bit 31 "not decided by the TF32 scores".
-constexpr unsigned int kInfoUnsafe = 1u << 31;
-constexpr unsigned int kInfoPair = 0u << 16;   // exactly the best and the runner-up
-constexpr unsigned int kInfoReach = 1u << 16;  // every centroid within 2 r_1 of the computed best
-[[maybe_unused]] constexpr unsigned int kInfoAll = 2u << 16;  // every centroid (kept for producers without a reach)
-
 struct ScParams {
     int64_t n;
     int64_t num_tiles;
@@ -95,6 +86,7 @@ struct ScParams {
     int stage_bytes;
     const float* X;
     int prefetch;  // tiles the producer asks into L2 ahead of its loads (0 = none)
+    int skip;      // development builds: bit 0 = the update warps add nothing, bit 1 = the assign warps skip the top-3
     const float* C;
     const float* cnorm;
     float* xnorm;  // [n] ||x||^2: written when xn_compute, read otherwise
@@ -129,15 +121,12 @@ __device__ __forceinline__ void mma_tf32_ss(uint32_t d_tmem, uint64_t a_desc, ui
         : "memory");
 }
 
-// acc (two packed floats) += v * m, m = {1, 1} or {0, 0}: one FFMA2 for two columns, no branch and no select.
-// (v * 1 + acc rounds exactly like v + acc.)
-__device__ __forceinline__ void fma2(unsigned long long& acc, unsigned long long v, unsigned long long m) {
+// acc (two packed floats) += v * w, w = 1 or 0: one FFMA2 for two columns, no branch and no select
+// (v * 1 + acc rounds exactly like v + acc).
+__device__ __forceinline__ void fma2s(unsigned long long& acc, unsigned long long v, float w) {
+    unsigned long long m;
+    asm("mov.b64 %0, {%1, %1};" : "=l"(m) : "f"(w));
     asm("fma.rn.f32x2 %0, %1, %2, %0;" : "+l"(acc) : "l"(v), "l"(m));
-}
-__device__ __forceinline__ unsigned long long pack2(float a, float b) {
-    unsigned long long r;
-    asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(a), "f"(b));
-    return r;
 }
 __device__ __forceinline__ float2 unpack2(unsigned long long v) {
     float2 r;
@@ -185,6 +174,15 @@ __device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&r)[16]) {
           "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
         : "r"(taddr)
         : "memory");
+}
+
+// Entry of the sorted row list: byte offset of row r inside a full atom (r*128 | swizzle) in the low half, inside the
+// narrow tail atom (row pitch 64 / 32 bytes) in the high half.
+__device__ __forceinline__ unsigned int perm_entry(int r, int tail_cols) {
+    const unsigned int full = (unsigned int)((r << 7) | ((r & 7) << 4));
+    const unsigned int tl = tail_cols == 16 ? (unsigned int)((r << 6) | (((r >> 1) & 3) << 4))
+                                            : (unsigned int)((r << 5) | (((r >> 2) & 1) << 4));
+    return full | (tl << 16);
 }
 
 // Byte offset of 16-byte chunk `chunk` (= float column / 4) of row r inside one tile stage.  Full atoms
@@ -274,205 +272,6 @@ __device__ __forceinline__ void top3_of_32(const float (&key)[32], float& o1, fl
     o3 = m3[0];
 }
 
-// The exact decisions are made by groups of kSubW lanes (two rows per warp at a time: the loads of a row are
-// independent, and the phase is bound by the latency of HBM, not by arithmetic).  sub = lane within the group,
-// gmask = the group's lanes.
-#ifndef B200KM_FIX_SUBW
-#define B200KM_FIX_SUBW 16
-#endif
-constexpr int kSubW = B200KM_FIX_SUBW;
-__device__ __forceinline__ float sqdist_f32(const float4* __restrict__ x4, const float4* __restrict__ c4, int nchunks,
-                                            int sub, unsigned gmask) {
-    float s = 0.f;
-    for (int ch = sub; ch < nchunks; ch += kSubW) {
-        const float4 xv = __ldg(x4 + ch), cv = __ldg(c4 + ch);
-        const float d0 = xv.x - cv.x, d1 = xv.y - cv.y, d2 = xv.z - cv.z, d3 = xv.w - cv.w;
-        s += fmaf(d0, d0, d1 * d1) + fmaf(d2, d2, d3 * d3);
-    }
-#pragma unroll
-    for (int o = kSubW / 2; o > 0; o >>= 1) s += __shfl_xor_sync(gmask, s, o);
-    return s;
-}
-__device__ __forceinline__ double sqdist_f64(const float* __restrict__ x, const float* __restrict__ c, int d, int sub,
-                                             unsigned gmask) {
-    double s = 0.0;
-    for (int i = sub; i < d; i += kSubW) {
-        const double df = (double)__ldg(x + i) - (double)__ldg(c + i);
-        s = fma(df, df, s);
-    }
-#pragma unroll
-    for (int o = kSubW / 2; o > 0; o >>= 1) s += __shfl_xor_sync(gmask, s, o);
-    return s;
-}
-
-// Exact label of one open row (one group of kSubW lanes): FP32 squared differences, float64 when even those tie; ties
-// keep the lowest index.  word = the row's verdict (computed best, runner-up, which centroids to look at).
-__device__ __forceinline__ int exact_label(const float* __restrict__ x, unsigned int word, int d, int k,
-                                           const float* __restrict__ C, const float* __restrict__ pd, int sub,
-                                           unsigned gmask) {
-    const int nchunks = d >> 2;
-    const int i1 = (int)(word & 255u), i2 = (int)((word >> 8) & 255u);
-    const unsigned int mode = word & (3u << 16);
-    const float4* x4 = reinterpret_cast<const float4*>(x);
-    int bi;
-    if (mode == kInfoPair) {
-        const int ja = min(i1, i2), jb = max(i1, i2);
-        const float sa = sqdist_f32(x4, reinterpret_cast<const float4*>(C + (size_t)ja * d), nchunks, sub, gmask);
-        const float sb = sqdist_f32(x4, reinterpret_cast<const float4*>(C + (size_t)jb * d), nchunks, sub, gmask);
-        bi = sb < sa ? jb : ja;
-        if (fabsf(sa - sb) <= 4e-6f * (sa + sb)) {
-            const double da = sqdist_f64(x, C + (size_t)ja * d, d, sub, gmask);
-            const double db = sqdist_f64(x, C + (size_t)jb * d, d, sub, gmask);
-            bi = db < da ? jb : ja;
-        }
-        return bi;
-    }
-    // every centroid, or those that can beat the computed best c_1 at all: ||c_1 - c_j|| <= 2 ||x - c_1||
-    float reach = FLT_MAX;
-    if (mode == kInfoReach)
-        reach = 2.f * sqrtf(sqdist_f32(x4, reinterpret_cast<const float4*>(C + (size_t)i1 * d), nchunks, sub, gmask)) * 1.0001f;
-    float f1 = FLT_MAX, f2 = FLT_MAX;
-    bi = i1;
-    for (int j = 0; j < k; ++j) {
-        if (j != i1 && reach < FLT_MAX && pd[(size_t)i1 * k + j] > reach) continue;
-        const float sum = sqdist_f32(x4, reinterpret_cast<const float4*>(C + (size_t)j * d), nchunks, sub, gmask);
-        if (sum < f1) {  // ascending index order: ties keep the lowest
-            f2 = f1;
-            f1 = sum;
-            bi = j;
-        } else {
-            f2 = fminf(f2, sum);
-        }
-    }
-    if (f2 < FLT_MAX && (f2 - f1) <= 4e-6f * (f1 + f2)) {
-        double bd = DBL_MAX;
-        for (int j = 0; j < k; ++j) {
-            if (j != i1 && reach < FLT_MAX && pd[(size_t)i1 * k + j] > reach) continue;
-            const double sum = sqdist_f64(x, C + (size_t)j * d, d, sub, gmask);
-            if (sum < bd) {
-                bd = sum;
-                bi = j;
-            }
-        }
-    }
-    return bi;
-}
-
-// Exact decision of the rows the screen left open, straight from HBM, and their contribution to the sums.
-// Every CTA owns a contiguous range of tiles and walks it in order, kFixTiles tiles at a time: the open rows come
-// from the bitmap (ascending row order), the warps decide them exactly, then thread t adds column t of every such
-// row - in list order - into the CTA's own float64 partial, which goes to the CTA's slot.  No atomics: the sums
-// do not depend on the order in which anything finishes.  These rows are few (C2: ~1 %), and keeping this code
-// out of the persistent kernel keeps that kernel's instruction stream hot.
-constexpr int kFixTiles = 32;
-constexpr int kFixCtasPerSm = 6;
-__global__ void __launch_bounds__(256) screen_fixup_kernel(const float* __restrict__ X, int64_t n, int d, int k,
-                                                           const float* __restrict__ C, const float* __restrict__ pd,
-                                                           const unsigned int* __restrict__ info,
-                                                           const unsigned int* __restrict__ bits, int64_t num_tiles,
-                                                           int32_t* __restrict__ labels, double* __restrict__ slots,
-                                                           int slot_stride, IterState* st, int honor_done) {
-    extern __shared__ double f_acc[];  // [k*d + k] when slots != nullptr
-    // per open row of the chunk: row offset inside the chunk (bits 18+) | the low 18 bits of its verdict word
-    __shared__ unsigned int s_ent[kFixTiles * kTileM];
-    __shared__ unsigned char s_lab[kFixTiles * kTileM];
-    __shared__ int s_warp[4];
-    if (honor_done && st->done) return;
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int acc_n = k * d + k;
-    if (slots)
-        for (int i = tid; i < acc_n; i += 256) f_acc[i] = 0.0;
-    const int64_t t0 = num_tiles * (int64_t)blockIdx.x / gridDim.x;
-    const int64_t t1 = num_tiles * (int64_t)(blockIdx.x + 1) / gridDim.x;
-    unsigned int decided = 0;
-    for (int64_t chunk = t0; chunk < t1; chunk += kFixTiles) {
-        const int nt = (int)((t1 - chunk) < kFixTiles ? (t1 - chunk) : kFixTiles);
-        const float* Xc = X + (size_t)chunk * kTileM * d;
-        // ---- the chunk's open rows, in ascending order (their verdict words are fetched here, all at once) ----
-        unsigned int w = 0;
-        if (tid < nt * 4) w = bits[chunk * 4 + tid];
-        int incl = __popc(w);
-#pragma unroll
-        for (int o = 1; o < 32; o <<= 1) {
-            const int t = __shfl_up_sync(0xffffffffu, incl, o);
-            if (lane >= o) incl += t;
-        }
-        __syncthreads();  // the previous chunk's lists are no longer read
-        if (warp < 4 && lane == 31) s_warp[warp] = incl;
-        __syncthreads();
-        int off = incl - __popc(w);
-        for (int q = 0; q < warp && q < 4; ++q) off += s_warp[q];
-        const int m = s_warp[0] + s_warp[1] + s_warp[2] + s_warp[3];
-        while (w) {
-            const int bpos = __ffs(w) - 1;
-            w &= w - 1;
-            const unsigned int roff = (unsigned int)(tid * 32 + bpos);
-            s_ent[off++] = (roff << 18) | (info[(size_t)chunk * kTileM + roff] & 0x3FFFFu);
-        }
-        __syncthreads();
-        // ---- exact labels: one group of kSubW lanes per row ----
-        {
-            const int sub = lane & (kSubW - 1);
-            const unsigned gmask = kSubW == 32 ? 0xffffffffu : ((1u << (kSubW & 31)) - 1u) << (lane & ~(kSubW - 1));
-            for (int i = tid / kSubW; i < m; i += 256 / kSubW) {
-                const unsigned int e = s_ent[i];
-                const unsigned int roff = e >> 18;
-                const int bi = exact_label(Xc + (size_t)roff * d, e & 0x3FFFFu, d, k, C, pd, sub, gmask);
-                if (sub == 0) {
-                    s_lab[i] = (unsigned char)bi;
-                    if (labels && bi != (int)(e & 255u)) labels[(size_t)chunk * kTileM + roff] = bi;
-                }
-            }
-        }
-        __syncthreads();
-        // ---- their rows into the partial sums, in list order: thread t owns column t, threads 128.. count ----
-        if (slots) {
-            if (tid < d) {
-                for (int i = 0; i < m; i += 8) {
-                    float v[8];
-                    int l[8];
-#pragma unroll
-                    for (int u = 0; u < 8; ++u) {
-                        const int ii = i + u < m ? i + u : m - 1;
-                        l[u] = s_lab[ii];
-                        v[u] = __ldg(Xc + (size_t)(s_ent[ii] >> 18) * d + tid);
-                    }
-#pragma unroll
-                    for (int u = 0; u < 8; ++u)
-                        if (i + u < m) f_acc[l[u] * d + tid] += (double)v[u];
-                }
-            } else if (tid >= 128 && tid - 128 < k) {
-                int c = 0;
-                for (int i = 0; i < m; ++i) c += (s_lab[i] == tid - 128);
-                f_acc[k * d + tid - 128] += (double)c;
-            }
-        }
-        decided += (unsigned int)m;
-    }
-    if (slots) {
-        __syncthreads();
-        double* slot = slots + (size_t)blockIdx.x * slot_stride;
-        for (int i = tid; i < acc_n; i += 256) slot[i] = f_acc[i];
-        if (tid == 0) slot[acc_n] = 0.0;
-    }
-    if (tid == 0 && decided) atomicAdd(&st->screen_refined, decided);
-}
-
-// acc[i] += sum over the slots of slot[i], in slot order: one warp per element, lane l adds slots l, l+32, ... and
-// the lanes meet in a fixed tree.
-__global__ void __launch_bounds__(256) slot_reduce_kernel(const double* __restrict__ slots, int nslots, int slot_stride,
-                                                          int len, double* __restrict__ acc, IterState* st, int honor_done) {
-    if (honor_done && st->done) return;
-    const int lane = threadIdx.x & 31;
-    const int i = blockIdx.x * 8 + (threadIdx.x >> 5);
-    if (i >= len) return;
-    double t = 0.0;
-    for (int sidx = lane; sidx < nslots; sidx += 32) t += slots[(size_t)sidx * slot_stride + i];
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) t += __shfl_down_sync(0xffffffffu, t, o);
-    if (lane == 0) acc[i] += t;
-}
-
 // ||x||^2 and ||x - trunc_tf32(x)||^2 of one row of the tile in `stage` (interleaved partial sums)
 __device__ __forceinline__ void acc_norms(const float4 v, float (&s)[4], float (&l)[4]) {
     const float e[4] = {v.x, v.y, v.z, v.w};
@@ -507,9 +306,10 @@ __global__ void __launch_bounds__(kThreads, 1)
     extern __shared__ uint8_t smem_raw[];
     // per assign group (= tile parity): bit r of s_mask[g][label][q] = row q*32 + r of the tile goes to `label`
     __shared__ __align__(16) unsigned int s_mask[2][kMaxKAcc + 1][4];  // row kMaxKAcc stays zero (free slots)
-    // per update warp: its rows of the current tile, ordered by (owned label, row); low half = byte offset of the
-    // row inside a full atom (r*128 | swizzle), high half = the same inside the narrow tail atom
-    __shared__ unsigned int s_list[kOwnBinsLater][kTileM + 8];
+    // per assign group: the tile's decided rows ordered by (label, row); low half of an entry = byte offset of the row
+    // inside a full atom (r*128 | swizzle), high half = the same inside the narrow tail atom
+    __shared__ unsigned int s_perm[2][kTileM + 4 * kMaxKAcc];  // runs padded to the update batch (<= 4)
+    __shared__ unsigned short s_base[2][kMaxKAcc];  // per label: start of its run in s_perm | rows << 8
     __shared__ unsigned int s_cntw[8][32];  // per assign warp: decided rows per label (lane = label)
     __shared__ double s_sumxn[16];          // per assign warp: sum of ||x||^2 over its rows
     uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
@@ -583,7 +383,7 @@ __global__ void __launch_bounds__(kThreads, 1)
 #pragma unroll 1
         for (int i = threadIdx.x; i < 2 * (kMaxKAcc + 1) * 4; i += kThreads) (&s_mask[0][0][0])[i] = 0;
 #pragma unroll 1
-        for (int i = threadIdx.x; i < kOwnBinsLater * (kTileM + 8); i += kThreads) (&s_list[0][0])[i] = 0;
+        for (int i = threadIdx.x; i < 2 * (kTileM + 4 * kMaxKAcc); i += kThreads) (&s_perm[0][0])[i] = 0;
         if (threadIdx.x < 8 * 32) (&s_cntw[0][0])[threadIdx.x] = 0;
     }
     tc_fence_before();
@@ -812,6 +612,13 @@ __global__ void __launch_bounds__(kThreads, 1)
                 xl = xn_s[(kMaxStages + s) * kTileM + row];
             }
             float b1 = FLT_MAX, b2 = FLT_MAX, b3 = FLT_MAX;
+#ifdef B200KM_ENABLE_TRACE
+            if (p.skip & 2) {
+                b1 = __uint_as_float(0x3f800000u | (uint32_t)(lane % p.k));
+                b2 = __uint_as_float(0x41800000u | (uint32_t)((lane + 1) % p.k));
+                b3 = 100.f;
+            } else
+#endif
 #pragma unroll 1
             for (int c0 = 0; c0 < p.k_pad; c0 += 32) {
                 uint32_t sc[32];
@@ -901,8 +708,36 @@ __global__ void __launch_bounds__(kThreads, 1)
                 if (lane < p.k) s_mask[sb][lane][q] = 0u;
                 __syncwarp();
                 if (bin >= 0) atomicOr(&s_mask[sb][bin][q], 1u << lane);
-                __syncwarp();
-                if (lane < p.k) cnt_lane += (unsigned int)__popc(s_mask[sb][lane][q]);
+                named_bar_sync(1 + g, 128);  // the group's four mask words of every label are complete
+                // lane = label: where its rows start in the sorted order, and where this warp's rows of it start
+                const uint4 m = *reinterpret_cast<const uint4*>(&s_mask[sb][lane][0]);  // rows >= k: zero
+                const int c0 = __popc(m.x), c1 = __popc(m.y), c2 = __popc(m.z), c3 = __popc(m.w);
+                const int tot = lane < p.k ? c0 + c1 + c2 + c3 : 0;
+                const int tot_pad = (tot + kUpdBatch - 1) / kUpdBatch * kUpdBatch;  // runs start at multiples of the batch
+                int incl = tot_pad;
+#pragma unroll
+                for (int o = 1; o < 32; o <<= 1) {
+                    const int v = __shfl_up_sync(0xffffffffu, incl, o);
+                    if (lane >= o) incl += v;
+                }
+                const int excl = incl - tot_pad;
+                if (q == 0) {
+                    s_base[sb][lane] = (unsigned short)(excl | (tot << 8));  // start | rows << 8
+                    if (tot_pad != tot) {
+                        // the padding repeats the label's last row (the highest set bit of its masks)
+                        const int qt = m.w ? 3 : m.z ? 2 : m.y ? 1 : 0;
+                        const unsigned int mt = m.w ? m.w : m.z ? m.z : m.y ? m.y : m.x;
+                        const int r = qt * 32 + 31 - __clz((int)mt);
+                        const unsigned int ent = perm_entry(r, p.tail_cols);
+                        for (int t = excl + tot; t < excl + tot_pad; ++t) s_perm[sb][t] = ent;
+                    }
+                }
+                const int mine = excl + (q > 0 ? c0 : 0) + (q > 1 ? c1 : 0) + (q > 2 ? c2 : 0);
+                const unsigned int mq = q == 0 ? m.x : q == 1 ? m.y : q == 2 ? m.z : m.w;
+                const int b = bin & 31;
+                const int pos = __shfl_sync(0xffffffffu, mine, b) + __popc(__shfl_sync(0xffffffffu, mq, b) & ((1u << lane) - 1u));
+                if (bin >= 0) s_perm[sb][pos] = perm_entry(row, p.tail_cols);
+                if (lane < p.k) cnt_lane += (unsigned int)__popc(mq);
                 __syncwarp();  // the warp's mask words precede its arrival; the update warps wait for all four
                 if (et == 0) trace_ev(p, it, 6);
                 if (lane == 0) mbar_arrive(s_full0 + 8u * sb);
@@ -949,6 +784,9 @@ __global__ void __launch_bounds__(kThreads, 1)
         const bool tail = a >= p.n_full;
         const int col_off = (tail ? p.n_full : a) * kAtomBytes;
         const int c16 = (tail ? (ch - p.n_full * 8) : (ch & 7)) << 4;
+        // a list entry is a byte offset inside an atom (< 16 KB, 16-byte granular): XOR with this constant applies the
+        // lane's swizzle and adds its atom's offset in one operation
+        const unsigned int xk = (unsigned int)(col_off | c16);
         unsigned long long acc[4][2];
 #pragma unroll
         for (int li = 0; li < 4; ++li) acc[li][0] = acc[li][1] = 0ull;
@@ -969,20 +807,6 @@ __global__ void __launch_bounds__(kThreads, 1)
                 acc[li][0] = acc[li][1] = 0ull;
             }
         };
-        // this lane's rows lane, 32 + lane, ... as list entries (offset in a full atom | offset in the tail atom << 16)
-        unsigned int enc[4];
-#pragma unroll
-        for (int w = 0; w < 4; ++w) {
-            const int r = w * 32 + lane;
-            const unsigned int full = (unsigned int)((r << 7) | ((r & 7) << 4));
-            const unsigned int tl = p.tail_cols == 16 ? (unsigned int)((r << 6) | (((r >> 1) & 3) << 4))
-                                                      : (unsigned int)((r << 5) | (((r >> 2) & 1) << 4));
-            enc[w] = full | (tl << 16);
-        }
-        const unsigned int lt = (1u << lane) - 1u;
-        unsigned int* list = s_list[u];
-        // the half of a list entry this lane's column chunk needs
-        const unsigned short* perm = reinterpret_cast<const unsigned short*>(list) + (tail ? 1 : 0);
         int64_t it = 0;
         int s = 0;
         uint32_t sph = 0;
@@ -990,52 +814,40 @@ __global__ void __launch_bounds__(kThreads, 1)
             const int sb = (int)(it & 1);
             mbar_wait(s_full0 + 8u * sb, (uint32_t)((it >> 1) & 1));
             if (ut == 0) trace_ev(p, it, 7);
-            // ---- the rows of the owned labels, label by label in ascending row order (= a stable sort) ----
-            int rb[5];
-            rb[0] = 0;
-#pragma unroll
-            for (int li = 0; li < 4; ++li) {
-                if (lab[li] == kMaxKAcc) {  // free slot (uniform)
-                    rb[li + 1] = rb[li];
-                    continue;
-                }
-                const uint4 m = *reinterpret_cast<const uint4*>(&s_mask[sb][lab[li]][0]);
-                const int c0 = __popc(m.x), c1 = __popc(m.y), c2 = __popc(m.z), c3 = __popc(m.w);
-                const int b0 = rb[li];
-                if ((m.x >> lane) & 1u) list[b0 + __popc(m.x & lt)] = enc[0];
-                if ((m.y >> lane) & 1u) list[b0 + c0 + __popc(m.y & lt)] = enc[1];
-                if ((m.z >> lane) & 1u) list[b0 + c0 + c1 + __popc(m.z & lt)] = enc[2];
-                if ((m.w >> lane) & 1u) list[b0 + c0 + c1 + c2 + __popc(m.w & lt)] = enc[3];
-                rb[li + 1] = b0 + c0 + c1 + c2 + c3;
-            }
-            __syncwarp();
-            if (lane == 0) mbar_arrive(s_empty0 + 8u * sb);  // the masks are consumed: the assign group may go on
-            if (ut == 0) trace_ev(p, it, 3);
+            // the half of a list entry this lane's column chunk needs
+            const unsigned short* perm = reinterpret_cast<const unsigned short*>(s_perm[sb]) + (tail ? 1 : 0);
             mbar_wait(x_full0 + 8u * s, sph);
-            const uint8_t* colp = smem + (size_t)s * stage_bytes + col_off;
+            const uint8_t* stagep = smem + (size_t)s * stage_bytes;
+            // Label by label, kUpdBatch list entries at a time.  The assign warps pad every label's run to a multiple
+            // of kUpdBatch with copies of its last entry: no bounds inside a batch, the copies get weight 0.
 #pragma unroll
             for (int li = 0; li < 4; ++li) {
-                const int end = rb[li + 1];
+                if (lab[li] == kMaxKAcc) continue;  // free slot (uniform)
+#ifdef B200KM_ENABLE_TRACE
+                if (p.skip & 1) continue;
+#endif
+                const unsigned int be = s_base[sb][lab[li]];  // start | rows << 8
+                int left = (int)(be >> 8);
+                const unsigned short* e = perm + 2 * (be & 255u);
 #pragma unroll 1
-                for (int base = rb[li]; base < end; base += kUpdBatch) {
-                    unsigned int w[kUpdBatch];
+                for (; left > 0; left -= kUpdBatch, e += 2 * kUpdBatch) {
                     ulonglong2 v[kUpdBatch];
-                    // rows past the end repeat the last one with weight 0 (always a row of this label)
 #pragma unroll
-                    for (int j = 0; j < kUpdBatch; ++j) w[j] = perm[2 * min(base + j, end - 1)];
-#pragma unroll
-                    for (int j = 0; j < kUpdBatch; ++j) v[j] = *reinterpret_cast<const ulonglong2*>(colp + (w[j] ^ c16));
+                    for (int j = 0; j < kUpdBatch; ++j)
+                        v[j] = *reinterpret_cast<const ulonglong2*>(stagep + ((unsigned int)e[2 * j] ^ xk));
 #pragma unroll
                     for (int j = 0; j < kUpdBatch; ++j) {
-                        const float on = base + j < end ? 1.f : 0.f;
-                        const unsigned long long m = pack2(on, on);
-                        fma2(acc[li][0], v[j].x, m);
-                        fma2(acc[li][1], v[j].y, m);
+                        const float on = j < left ? 1.f : 0.f;
+                        fma2s(acc[li][0], v[j].x, on);
+                        fma2s(acc[li][1], v[j].y, on);
                     }
                 }
             }
             __syncwarp();
-            if (lane == 0) mbar_arrive(x_empty0 + 8u * s);
+            if (lane == 0) {
+                mbar_arrive(s_empty0 + 8u * sb);
+                mbar_arrive(x_empty0 + 8u * s);
+            }
             if (lane == 0) trace_ev(p, it, 8 + u);
             if ((it & 7) == 7 || tile + tile_step >= p.num_tiles) fold();  // single (rare) fold site
             if (++s == S) {
@@ -1209,9 +1021,6 @@ int screen_pass(TcWorkspace* ws, const float* X, int64_t n, int d, int k, const 
     const int64_t num_tiles = (n + kTileM - 1) / kTileM;
     const int acc_n = k * d + k;
     const int slot_stride = (acc_n + 1 + 7) & ~7;
-    int64_t fix_grid = (num_tiles + kFixTiles - 1) / kFixTiles;
-    if (fix_grid > kNumSMs * kFixCtasPerSm) fix_grid = kNumSMs * kFixCtasPerSm;
-    if (fix_grid < 1) fix_grid = 1;
     {
         const size_t need_bits = sizeof(unsigned int) * 4 * (size_t)(num_tiles + 1);
         if (need_bits > ws->bits_cap) {
@@ -1287,9 +1096,11 @@ int screen_pass(TcWorkspace* ws, const float* X, int64_t n, int d, int k, const 
     p.stacked = (2 * pl.k_pad * kMaxND <= 512) ? 1 : 0;
     p.stage_bytes = pl.stage_bytes;
     p.X = X;
-    p.prefetch = 3;
+    p.prefetch = 0;
+    p.skip = 0;
 #ifdef B200KM_ENABLE_TRACE
     if (const char* e = getenv("B200KM_PREFETCH")) p.prefetch = atoi(e);
+    if (const char* e = getenv("B200KM_SKIP")) p.skip = atoi(e);
 #endif
     p.C = C;
     p.cnorm = cnorm;
@@ -1340,19 +1151,9 @@ int screen_pass(TcWorkspace* ws, const float* X, int64_t n, int d, int k, const 
         snprintf(g_sc_err, sizeof(g_sc_err), "screen kernel launch failed: %s", cudaGetErrorString(err));
         return 1;
     }
-    {
-        // exact pass over the open rows (deterministic per-CTA partials), then all slots in a fixed order
-        double* fix_slots = acc ? (double*)ws->d_slots + (size_t)grid * slot_stride : nullptr;
-        const size_t fsm = acc ? sizeof(double) * (size_t)acc_n : 0;
-        screen_fixup_kernel<<<(unsigned)fix_grid, 256, fsm, s>>>(X, n, d, k, C, (const float*)ws->d_pd, info,
-                                                                (const unsigned int*)ws->d_bits, num_tiles, labels,
-                                                                fix_slots, slot_stride, st, honor_done ? 1 : 0);
-        count_launch();
-        if (acc) {
-            slot_reduce_kernel<<<(acc_n + 1 + 7) / 8, 256, 0, s>>>((const double*)ws->d_slots, (int)(grid + fix_grid),
-                                                                  slot_stride, acc_n + 1, acc, st, honor_done ? 1 : 0);
-            count_launch();
-        }
+    if (screen_fixup(ws, X, n, d, k, C, info, num_tiles, labels, acc, (int)grid, slot_stride, st, honor_done, s)) {
+        snprintf(g_sc_err, sizeof(g_sc_err), "exact pass of the screen kernel failed: %s", fixup_last_error());
+        return 1;
     }
     KT(3);
 #ifdef B200KM_ENABLE_TRACE

@@ -38,7 +38,6 @@ using namespace tcx;
 
 thread_local char g_tc_err[512] = "";
 
-constexpr int kTileM = 128;
 constexpr int kAtomBytes = kTileM * 128;  // one full K-atom of an X tile: 128 rows x 32 floats
 constexpr int kRing = 4;                  // TMEM ring slots for (x_hi | x_lo) atoms, 64 columns each
 constexpr int kRingCol0 = 256;            // ring occupies TMEM columns [256, 512)
@@ -790,6 +789,11 @@ void tc_free(TcWorkspace* ws) {
     if (ws->d_pd) cudaFree(ws->d_pd);
     if (ws->d_bits) cudaFree(ws->d_bits);
     if (ws->d_slots) cudaFree(ws->d_slots);
+    if (ws->d_open_rows) cudaFree(ws->d_open_rows);
+    if (ws->d_open_info) cudaFree(ws->d_open_info);
+    if (ws->d_open_blk) cudaFree(ws->d_open_blk);
+    ws->d_open_rows = ws->d_open_info = ws->d_open_blk = nullptr;
+    ws->open_cap = ws->open_blk_cap = 0;
     ws->d_buf = nullptr;
     ws->d_pd = nullptr;
     ws->d_bits = nullptr;

@@ -13,7 +13,34 @@ struct TcWorkspace {
     size_t bits_cap = 0;
     void* d_slots = nullptr;  // per-CTA float64 partial sums of the screen kernel and its exact pass
     size_t slots_cap = 0;
+    // exact pass (kernels_fixup.cu): the open rows as one list in row order (row index, verdict word), the popcount
+    // of every block of bitmap words and its prefix, the number of open rows
+    void* d_open_rows = nullptr;
+    void* d_open_info = nullptr;
+    size_t open_cap = 0;  // entries
+    void* d_open_blk = nullptr;
+    size_t open_blk_cap = 0;  // blocks
 };
+
+constexpr int kTileM = 128;  // rows of a tile of the screen kernel = rows covered by 4 bitmap words
+// Per-row verdict written by the screen kernel: bits 0-7 the computed best centroid (the row's provisional
+// label, already counted in the sums), bits 8-15 the runner-up, bits 16-17 what the exact pass has to look at,
+// bit 31 "not decided by the TF32 scores".
+constexpr unsigned int kInfoUnsafe = 1u << 31;
+constexpr unsigned int kInfoPair = 0u << 16;   // exactly the best and the runner-up
+constexpr unsigned int kInfoReach = 1u << 16;  // every centroid within 2 r_1 of the computed best
+[[maybe_unused]] constexpr unsigned int kInfoAll = 2u << 16;  // every centroid (kept for producers without a reach)
+
+constexpr int kFixCtasPerSm = 4;  // CTAs (= partial-sum slots) of the exact pass per SM
+// Exact decision of the rows the screen kernel left open and their contribution to the sums (kernels_fixup.cu): reads
+// the bitmap ws->d_bits and the verdict words `info`, writes labels (where they change) and, when acc != nullptr, one
+// float64 partial per CTA into ws->d_slots behind the screen kernel's `screen_slots` slots, then adds all slots into
+// acc in slot order.
+int screen_fixup(TcWorkspace* ws, const float* X, int64_t n, int d, int k, const float* C, const unsigned int* info,
+                 int64_t num_tiles, int32_t* labels, double* acc, int screen_slots, int slot_stride, IterState* st,
+                 bool honor_done, cudaStream_t s);
+const char* fixup_last_error();
+
 
 bool tc_supported(const float* X, int d, int k, bool with_acc);
 int tc_max_d();
