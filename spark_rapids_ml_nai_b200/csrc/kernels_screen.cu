@@ -121,12 +121,9 @@ __device__ __forceinline__ void mma_tf32_ss(uint32_t d_tmem, uint64_t a_desc, ui
         : "memory");
 }
 
-// acc (two packed floats) += v * w, w = 1 or 0: one FFMA2 for two columns, no branch and no select
-// (v * 1 + acc rounds exactly like v + acc).
-__device__ __forceinline__ void fma2s(unsigned long long& acc, unsigned long long v, float w) {
-    unsigned long long m;
-    asm("mov.b64 %0, {%1, %1};" : "=l"(m) : "f"(w));
-    asm("fma.rn.f32x2 %0, %1, %2, %0;" : "+l"(acc) : "l"(v), "l"(m));
+// acc (two packed floats) += v: one FADD2 for two columns
+__device__ __forceinline__ void add2(unsigned long long& acc, unsigned long long v) {
+    asm("add.rn.f32x2 %0, %0, %1;" : "+l"(acc) : "l"(v));
 }
 __device__ __forceinline__ float2 unpack2(unsigned long long v) {
     float2 r;
@@ -308,7 +305,7 @@ __global__ void __launch_bounds__(kThreads, 1)
     __shared__ __align__(16) unsigned int s_mask[2][kMaxKAcc + 1][4];  // row kMaxKAcc stays zero (free slots)
     // per assign group: the tile's decided rows ordered by (label, row); low half of an entry = byte offset of the row
     // inside a full atom (r*128 | swizzle), high half = the same inside the narrow tail atom
-    __shared__ unsigned int s_perm[2][kTileM + 4 * kMaxKAcc];  // runs padded to the update batch (<= 4)
+    __shared__ __align__(16) unsigned int s_perm[2][kTileM + 4 * kMaxKAcc];  // runs start at multiples of the update batch
     __shared__ unsigned short s_base[2][kMaxKAcc];  // per label: start of its run in s_perm | rows << 8
     __shared__ unsigned int s_cntw[8][32];  // per assign warp: decided rows per label (lane = label)
     __shared__ double s_sumxn[16];          // per assign warp: sum of ||x||^2 over its rows
@@ -713,7 +710,8 @@ __global__ void __launch_bounds__(kThreads, 1)
                 const uint4 m = *reinterpret_cast<const uint4*>(&s_mask[sb][lane][0]);  // rows >= k: zero
                 const int c0 = __popc(m.x), c1 = __popc(m.y), c2 = __popc(m.z), c3 = __popc(m.w);
                 const int tot = lane < p.k ? c0 + c1 + c2 + c3 : 0;
-                const int tot_pad = (tot + kUpdBatch - 1) / kUpdBatch * kUpdBatch;  // runs start at multiples of the batch
+                const int tot_pad = (tot + kUpdBatch - 1) / kUpdBatch * kUpdBatch;  // runs start at multiples of the batch (one
+                                                                                   // aligned load fetches its entries)
                 int incl = tot_pad;
 #pragma unroll
                 for (int o = 1; o < 32; o <<= 1) {
@@ -721,17 +719,7 @@ __global__ void __launch_bounds__(kThreads, 1)
                     if (lane >= o) incl += v;
                 }
                 const int excl = incl - tot_pad;
-                if (q == 0) {
-                    s_base[sb][lane] = (unsigned short)(excl | (tot << 8));  // start | rows << 8
-                    if (tot_pad != tot) {
-                        // the padding repeats the label's last row (the highest set bit of its masks)
-                        const int qt = m.w ? 3 : m.z ? 2 : m.y ? 1 : 0;
-                        const unsigned int mt = m.w ? m.w : m.z ? m.z : m.y ? m.y : m.x;
-                        const int r = qt * 32 + 31 - __clz((int)mt);
-                        const unsigned int ent = perm_entry(r, p.tail_cols);
-                        for (int t = excl + tot; t < excl + tot_pad; ++t) s_perm[sb][t] = ent;
-                    }
-                }
+                if (q == 0) s_base[sb][lane] = (unsigned short)(excl | (tot << 8));  // start | rows << 8
                 const int mine = excl + (q > 0 ? c0 : 0) + (q > 1 ? c1 : 0) + (q > 2 ? c2 : 0);
                 const unsigned int mq = q == 0 ? m.x : q == 1 ? m.y : q == 2 ? m.z : m.w;
                 const int b = bin & 31;
@@ -787,6 +775,7 @@ __global__ void __launch_bounds__(kThreads, 1)
         // a list entry is a byte offset inside an atom (< 16 KB, 16-byte granular): XOR with this constant applies the
         // lane's swizzle and adds its atom's offset in one operation
         const unsigned int xk = (unsigned int)(col_off | c16);
+        const int half_shift = tail ? 16 : 0;  // the half of a list entry this lane's column chunk needs
         unsigned long long acc[4][2];
 #pragma unroll
         for (int li = 0; li < 4; ++li) acc[li][0] = acc[li][1] = 0ull;
@@ -814,12 +803,9 @@ __global__ void __launch_bounds__(kThreads, 1)
             const int sb = (int)(it & 1);
             mbar_wait(s_full0 + 8u * sb, (uint32_t)((it >> 1) & 1));
             if (ut == 0) trace_ev(p, it, 7);
-            // the half of a list entry this lane's column chunk needs
-            const unsigned short* perm = reinterpret_cast<const unsigned short*>(s_perm[sb]) + (tail ? 1 : 0);
             mbar_wait(x_full0 + 8u * s, sph);
             const uint8_t* stagep = smem + (size_t)s * stage_bytes;
-            // Label by label, kUpdBatch list entries at a time.  The assign warps pad every label's run to a multiple
-            // of kUpdBatch with copies of its last entry: no bounds inside a batch, the copies get weight 0.
+            // Label by label, kUpdBatch list entries at a time; every label's run starts at a multiple of kUpdBatch.
 #pragma unroll
             for (int li = 0; li < 4; ++li) {
                 if (lab[li] == kMaxKAcc) continue;  // free slot (uniform)
@@ -828,18 +814,25 @@ __global__ void __launch_bounds__(kThreads, 1)
 #endif
                 const unsigned int be = s_base[sb][lab[li]];  // start | rows << 8
                 int left = (int)(be >> 8);
-                const unsigned short* e = perm + 2 * (be & 255u);
+                // four list entries with one broadcast load (runs start at multiples of four entries); rows past the
+                // end of the run are not loaded at all: shared-memory bandwidth is what the kernel runs out of
+                const uint4* e4 = reinterpret_cast<const uint4*>(s_perm[sb] + (be & 255u));
+                static_assert(kUpdBatch == 4, "the update warps fetch four list entries per load");
 #pragma unroll 1
-                for (; left > 0; left -= kUpdBatch, e += 2 * kUpdBatch) {
-                    ulonglong2 v[kUpdBatch];
+                for (; left > 0; left -= 4, ++e4) {
+                    const uint4 ent = *e4;
+                    const unsigned int w[4] = {ent.x, ent.y, ent.z, ent.w};
+                    ulonglong2 v[4];
 #pragma unroll
-                    for (int j = 0; j < kUpdBatch; ++j)
-                        v[j] = *reinterpret_cast<const ulonglong2*>(stagep + ((unsigned int)e[2 * j] ^ xk));
+                    for (int j = 0; j < 4; ++j) {
+                        v[j] = make_ulonglong2(0ull, 0ull);
+                        if (j < left)
+                            v[j] = *reinterpret_cast<const ulonglong2*>(stagep + (((w[j] >> half_shift) & 0xffffu) ^ xk));
+                    }
 #pragma unroll
-                    for (int j = 0; j < kUpdBatch; ++j) {
-                        const float on = j < left ? 1.f : 0.f;
-                        fma2s(acc[li][0], v[j].x, on);
-                        fma2s(acc[li][1], v[j].y, on);
+                    for (int j = 0; j < 4; ++j) {
+                        add2(acc[li][0], v[j].x);
+                        add2(acc[li][1], v[j].y);
                     }
                 }
             }
