@@ -131,17 +131,6 @@ __device__ __forceinline__ float2 unpack2(unsigned long long v) {
     return r;
 }
 
-__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&r)[32]) {
-    asm volatile(
-        "tcgen05.ld.sync.aligned.32x32b.x32.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
-        "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
-        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
-          "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]),
-          "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]),
-          "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
-        : "r"(taddr)
-        : "memory");
-}
 
 // The assign warps' waits: inline (a call would make the compiler wait for every load in flight first, and these
 // warps keep the next tile's row norms in flight across their waits).
@@ -237,24 +226,25 @@ __global__ void __launch_bounds__(128) screen_prep_kernel(const float* __restric
     if (lane == 0) pd[pair] = sqrtf(s) * (1.f + 1e-5f) + 1e-30f;
 }
 
-// The three smallest of 32 keys by a tournament of sorted lists (independent operations, short dependency
+// The three smallest of N (4, 8 or 16) keys by a tournament of sorted lists (independent operations, short dependency
 // chains): pairs -> triples -> ...; the third smallest of two sorted triples is min(a3, b3, max(a1,b2), max(a2,b1)).
-__device__ __forceinline__ void top3_of_32(const float (&key)[32], float& o1, float& o2, float& o3) {
-    float m1[16], m2[16], m3[8];
+template <int N>
+__device__ __forceinline__ void top3_of(const float (&key)[N], float& o1, float& o2, float& o3) {
+    float m1[N / 2], m2[N / 2], m3[N / 4];
 #pragma unroll
-    for (int i = 0; i < 16; ++i) {
+    for (int i = 0; i < N / 2; ++i) {
         m1[i] = fminf(key[2 * i], key[2 * i + 1]);
         m2[i] = fmaxf(key[2 * i], key[2 * i + 1]);
     }
 #pragma unroll
-    for (int i = 0; i < 8; ++i) {  // two sorted pairs -> sorted triple
+    for (int i = 0; i < N / 4; ++i) {  // two sorted pairs -> sorted triple
         const float a1 = m1[2 * i], a2 = m2[2 * i], b1 = m1[2 * i + 1], b2 = m2[2 * i + 1];
         m1[i] = fminf(a1, b1);
         m2[i] = fminf(fmaxf(a1, b1), fminf(a2, b2));
         m3[i] = fminf(fmaxf(a1, b2), fmaxf(a2, b1));
     }
 #pragma unroll
-    for (int nn = 8; nn > 1; nn >>= 1) {
+    for (int nn = N / 4; nn > 1; nn >>= 1) {
 #pragma unroll
         for (int i = 0; i < nn / 2; ++i) {
             const float a1 = m1[2 * i], a2 = m2[2 * i], a3 = m3[2 * i];
@@ -267,6 +257,65 @@ __device__ __forceinline__ void top3_of_32(const float (&key)[32], float& o1, fl
     o1 = m1[0];
     o2 = m2[0];
     o3 = m3[0];
+}
+template <int N>
+__device__ __forceinline__ void tmem_ldn(uint32_t taddr, uint32_t (&r)[N]);
+template <>
+__device__ __forceinline__ void tmem_ldn<16>(uint32_t taddr, uint32_t (&r)[16]) {
+    tmem_ld16(taddr, r);
+}
+template <>
+__device__ __forceinline__ void tmem_ldn<4>(uint32_t taddr, uint32_t (&r)[4]) {
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x4.b32 {%0, %1, %2, %3}, [%4];"
+                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3])
+                 : "r"(taddr)
+                 : "memory");
+}
+template <>
+__device__ __forceinline__ void tmem_ldn<8>(uint32_t taddr, uint32_t (&r)[8]) {
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
+                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7])
+                 : "r"(taddr)
+                 : "memory");
+}
+// N columns [c0, c0 + N) of this thread's row: scores from TMEM (the two column ranges of a stacked pass added),
+// keys ||c_j||^2 - 2 x^.c_j with the centroid index in the low mantissa bits, their three smallest merged into
+// the running sorted triple (b1, b2, b3).
+template <int N>
+__device__ __forceinline__ void score_chunk(uint32_t taddr, int c0, int lo_off, bool stacked, const float* cn_s,
+                                            uint32_t idx_mask, float& b1, float& b2, float& b3) {
+    uint32_t sc[N];
+    tmem_ldn<N>(taddr + c0, sc);
+    if (stacked) {
+        uint32_t sl[N];
+        tmem_ldn<N>(taddr + lo_off + c0, sl);
+        tmem_wait_ld();
+#pragma unroll
+        for (int j = 0; j < N; ++j) sc[j] = __float_as_uint(__uint_as_float(sc[j]) + __uint_as_float(sl[j]));
+    } else {
+        tmem_wait_ld();
+    }
+    float key[N];
+    const float4* cn4 = reinterpret_cast<const float4*>(cn_s + c0);
+#pragma unroll
+    for (int j4 = 0; j4 < N / 4; ++j4) {
+        const float4 c = cn4[j4];
+        const float cc[4] = {c.x, c.y, c.z, c.w};
+#pragma unroll
+        for (int t = 0; t < 4; ++t) {
+            const int j = j4 * 4 + t;
+            const float dj = fmaf(-2.f, __uint_as_float(sc[j]), cc[t]);  // padded columns: FLT_MAX
+            key[j] = __uint_as_float((__float_as_uint(dj) & ~idx_mask) | (uint32_t)(c0 + j));
+        }
+    }
+    float t1, t2, t3;
+    top3_of<N>(key, t1, t2, t3);
+    const float n1 = fminf(b1, t1);
+    const float n2 = fminf(fmaxf(b1, t1), fminf(b2, t2));
+    const float n3 = fminf(fminf(b3, t3), fminf(fmaxf(b1, t2), fmaxf(b2, t1)));
+    b1 = n1;
+    b2 = n2;
+    b3 = n3;
 }
 
 // ||x||^2 and ||x - trunc_tf32(x)||^2 of one row of the tile in `stage` (interleaved partial sums)
@@ -308,7 +357,6 @@ __global__ void __launch_bounds__(kThreads, 1)
     __shared__ __align__(16) unsigned int s_perm[2][kTileM + 4 * kMaxKAcc];  // runs start at multiples of the update batch
     __shared__ unsigned short s_base[2][kMaxKAcc];  // per label: start of its run in s_perm | rows << 8
     __shared__ unsigned int s_cntw[8][32];  // per assign warp: decided rows per label (lane = label)
-    __shared__ double s_sumxn[16];          // per assign warp: sum of ||x||^2 over its rows
     uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
     const uint32_t smem_base = smem_u32(smem);
 
@@ -376,7 +424,6 @@ __global__ void __launch_bounds__(kThreads, 1)
 #pragma unroll 1
             for (int i = threadIdx.x; i < p.k * p.d + p.k; i += kThreads) sacc_init[i] = 0.0;
         }
-        if (threadIdx.x < 16) s_sumxn[threadIdx.x] = 0.0;
 #pragma unroll 1
         for (int i = threadIdx.x; i < 2 * (kMaxKAcc + 1) * 4; i += kThreads) (&s_mask[0][0][0])[i] = 0;
 #pragma unroll 1
@@ -569,8 +616,10 @@ __global__ void __launch_bounds__(kThreads, 1)
         const float* nb_s = pd_s + 32 * 32;                        // per centroid: nearest, second nearest, who
         const int sb = g;
 
-        double sum_xn = 0.0;
         unsigned int cnt_lane = 0u;  // lane = label: rows this warp has decided for it
+        // the centroid index rides in the low mantissa bits of a key: 5 bits (2^-18 of the key) for k <= 32, else 7
+        const uint32_t idx_mask = p.k_pad <= 32 ? 31u : 127u;
+        const float idx_eps = p.k_pad <= 32 ? 4e-6f : 1.6e-5f;
         int s = g % S;
         uint32_t sph = (uint32_t)((g / S) & 1);  // g < 4: cheap, once
         int64_t tile = first_tile + (int64_t)g * tile_step;
@@ -601,8 +650,7 @@ __global__ void __launch_bounds__(kThreads, 1)
             const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(db * dcols);
             int label = 0;
             unsigned int verdict = 0;  // this row's info word
-            // ---- 32 scores at a time into registers; keys D_j = ||x||^2 + ||c_j||^2 - 2 x^.c_j carry the centroid
-            // index in their 7 low mantissa bits (a perturbation below 2^-16 |D_j|, covered by the bound) ----
+            // ---- the scores a chunk of columns at a time into registers (score_chunk) ----
             if (p.xn_compute) {
                 sc_wait(xn_full0 + 8u * s, sph);
                 xn = xn_s[s * kTileM + row];
@@ -616,56 +664,33 @@ __global__ void __launch_bounds__(kThreads, 1)
                 b3 = 100.f;
             } else
 #endif
+            {
+                // the real columns only: 16 at a time, then 8 and 4 for the remainder (k = 20: 16 + 4, not 32)
+                const int kcols = (p.k + 3) & ~3;
+                int c0 = 0;
 #pragma unroll 1
-            for (int c0 = 0; c0 < p.k_pad; c0 += 32) {
-                uint32_t sc[32];
-                if (stacked) {  // x^.c_hi + x^.c_lo: the two column ranges, 16 columns at a time
-#pragma unroll
-                    for (int hh = 0; hh < 2; ++hh) {
-                        uint32_t sh[16], sl[16];
-                        tmem_ld16(taddr + c0 + 16 * hh, sh);
-                        tmem_ld16(taddr + p.k_pad + c0 + 16 * hh, sl);
-                        tmem_wait_ld();
-#pragma unroll
-                        for (int j = 0; j < 16; ++j)
-                            sc[16 * hh + j] = __float_as_uint(__uint_as_float(sh[j]) + __uint_as_float(sl[j]));
-                    }
-                } else {
-                    tmem_ld32(taddr + c0, sc);
-                    tmem_wait_ld();
+                for (; c0 + 16 <= kcols; c0 += 16) score_chunk<16>(taddr, c0, p.k_pad, stacked, cn_s, idx_mask, b1, b2, b3);
+                if (c0 + 8 <= kcols) {
+                    score_chunk<8>(taddr, c0, p.k_pad, stacked, cn_s, idx_mask, b1, b2, b3);
+                    c0 += 8;
                 }
-                float key[32];
-                const float4* cn4 = reinterpret_cast<const float4*>(cn_s + c0);
-#pragma unroll
-                for (int j4 = 0; j4 < 8; ++j4) {
-                    const float4 c = cn4[j4];
-                    const float cc[4] = {c.x, c.y, c.z, c.w};
-#pragma unroll
-                    for (int t = 0; t < 4; ++t) {
-                        const int j = j4 * 4 + t;
-                        const float dj = fmaf(-2.f, __uint_as_float(sc[j]), cc[t] + xn);  // padded columns: FLT_MAX
-                        key[j] = __uint_as_float((__float_as_uint(dj) & ~127u) | (uint32_t)(c0 + j));
-                    }
-                }
-                float t1, t2, t3;
-                top3_of_32(key, t1, t2, t3);
-                // merge the chunk's sorted triple into the running one
-                const float n1 = fminf(b1, t1);
-                const float n2 = fminf(fmaxf(b1, t1), fminf(b2, t2));
-                const float n3 = fminf(fminf(b3, t3), fminf(fmaxf(b1, t2), fmaxf(b2, t1)));
-                b1 = n1;
-                b2 = n2;
-                b3 = n3;
+                if (c0 < kcols) score_chunk<4>(taddr, c0, p.k_pad, stacked, cn_s, idx_mask, b1, b2, b3);
             }
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(d_empty0 + 8u * db);  // the score buffer is free again
-            const int i1 = (int)(__float_as_uint(b1) & 127u), i2 = (int)(__float_as_uint(b2) & 127u);
+            const int i1 = (int)(__float_as_uint(b1) & idx_mask), i2 = (int)(__float_as_uint(b2) & idx_mask);
             label = i1;
+            // the keys are ||c_j||^2 - 2 x^.c_j: the row's own ||x||^2 does not change their order and is added to
+            // the three that matter only.  The index bits perturb a key by less than idx_eps of its magnitude.
+            const float kmag12 = fabsf(b1) + fabsf(b2), kmag3 = fabsf(b3);
+            b1 += xn;
+            b2 += xn;
+            b3 += xn;
             // safety test (see the file header); every quantity is an upper bound
             const float scale = xn + cmax;
             const float t = p.tol_x * sqrt_up(xl);  // >= ||x - x^||
-            const float eps = p.eps_rel * scale + 1.6e-5f * (fabsf(b1) + fabsf(b2));
+            const float eps = p.eps_rel * scale + idx_eps * kmag12;
             const float r1 = sqrt_up(fmaxf(b1, 0.f) + p.abs_rel * scale);
             const float safe = 4.f * t * r1 + eps;
             const float margin = b2 - b1;
@@ -676,7 +701,7 @@ __global__ void __launch_bounds__(kThreads, 1)
             const bool pair_ok = margin >= fminf(2.f * t * pd12 + eps, safe);
             const float others = (__float_as_int(nb_s[2 * kMaxK + i1]) == i2) ? nb_s[kMaxK + i1] : nb_s[i1];
             const bool third = valid && p.k > 2 && others <= 2.f * r1 &&
-                               (b3 - b1) < safe + 1.6e-5f * fabsf(b3);  // a third candidate cannot be excluded
+                               (b3 - b1) < safe + idx_eps * kmag3;  // a third candidate cannot be excluded
             const bool amb = (valid && p.k > 1 && !pair_ok) || third;
             verdict = (unsigned)i1 | ((unsigned)i2 << 8) | (amb ? kInfoUnsafe | (third ? kInfoReach : kInfoPair) : 0u);
 
@@ -685,7 +710,6 @@ __global__ void __launch_bounds__(kThreads, 1)
             if (valid) {
                 if (amb) p.info[grow] = verdict;
                 if (p.labels) p.labels[grow] = label;
-                sum_xn += (double)xn;
             }
             {
                 // open rows: one bitmap word per warp and tile (the exact pass finds them without reading a word per row)
@@ -739,11 +763,6 @@ __global__ void __launch_bounds__(kThreads, 1)
                 sph ^= 1u;
             }
         }
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) {
-            sum_xn += __shfl_xor_sync(0xffffffffu, sum_xn, o);
-        }
-        if (lane == 0 && p.acc) s_sumxn[warp - kAssignWarp0] = sum_xn;
         if (p.acc) s_cntw[warp - kAssignWarp0][lane] = cnt_lane;
     } else if (p.acc && (warp >= kUpdateWarp0 || warp < kAssignWarp0)) {
         // ======================================== update ========================================
@@ -873,11 +892,7 @@ __global__ void __launch_bounds__(kThreads, 1)
             for (int w = 0; w < 8; ++w) c += s_cntw[w][threadIdx.x];
             slot[p.k * p.d + threadIdx.x] = (double)c;
         }
-        if (threadIdx.x == 0) {
-            double t = 0.0;
-            for (int w = 0; w < 16; ++w) t += s_sumxn[w];
-            slot[acc_n] = t;
-        }
+        if (threadIdx.x == 0) slot[acc_n] = 0.0;  // the inertia slot: this pass has no per-row distances
     }
     if (warp == 1) {
         asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512));
