@@ -4,8 +4,8 @@
 // in shared memory,
 //   1. scores it against the centroids on the tensor cores straight from shared memory: A = the raw FP32
 //      tile (the tensor core reads the top 19 bits of each word, i.e. x truncated to TF32), B = the stacked
-//      TF32 split [c_hi ; c_lo] of the centroids, FP32 accumulation in TMEM; the assign warps form
-//      D_j = ||x||^2 + ||c_j||^2 - 2 x^.c_j;
+//      TF32 split [c_hi ; c_lo] of the centroids, FP32 accumulation in TMEM; the assign warps order the centroids by
+//      ||c_j||^2 - 2 x^.c_j and form D_j = ||x||^2 + ||c_j||^2 - 2 x^.c_j for the three nearest;
 //   2. decides which rows the TF32 view of x decides.  With x^ = trunc(x) the error of a MARGIN D_a - D_b is
 //      2 (x - x^).(c_a - c_b) plus FP32 rounding, hence bounded by 2 ||x - x^|| ||c_a - c_b|| + eps: it scales
 //      with the distance between the two centroids (a k x k table), not with their norms, and ||x - x^|| is the
@@ -14,13 +14,14 @@
 //      when its runner-up margin exceeds the pair's bound and either no other centroid is that close to c_1
 //      (each centroid's nearest-neighbour distances) or the third-best margin exceeds 4 ||x - x^|| r_1 + eps.
 //      Every row leaves a verdict word; the open rows keep the computed best as a provisional label;
-//   3. adds the decided rows (exact FP32 data, not the TF32 view) into per-cluster sums: the assign warps leave one
-//      mask word per (label, warp), the update warps turn the masks of the labels they own into row lists and add
-//      the rows in ascending order into FP32 registers / float64 shared memory.
-// screen_fixup_kernel then decides the open rows exactly from HBM (FP32 squared differences, float64 when even
-// those tie) and moves a row between the float64 sums when its exact label differs - labels and sums are exact
-// for every row.  Keeping that rarely executed code out of the persistent kernel matters: inside it, one such
-// row cost 1400-2400 cycles of an assign warp (instruction fetch of cold code), 0.9 % of the rows cost 30 %.
+//   3. adds the decided rows (exact FP32 data, not the TF32 view) into per-cluster sums: every row ORs its bit into
+//      its label's mask word (shared-memory atomic OR: order-free), the assign group turns the masks into the list of
+//      the tile's rows ordered by (label, row) - no comparison sort: positions are popcounts -, and the update warps
+//      add each label's run in that order into FP32 registers / float64 shared memory.
+// The exact pass (kernels_fixup.cu) then decides the open rows exactly (FP32 squared differences, float64 when even
+// those tie) and adds them - labels and sums are exact for every row.  Keeping that rarely executed code out of the
+// persistent kernel matters: inside it, one such row cost 1400-2400 cycles of an assign warp (instruction fetch of
+// cold code), 0.9 % of the rows cost 30 %.
 // The pass produces no per-row distances; a caller that wants the inertia of the pass (b200km_lloyd_step) takes one
 // more pass of exact per-row differences (rowdist_kernel) rather than the cancelling identity
 // sum ||x||^2 - 2 sum c.S + sum n ||c||^2.
@@ -35,12 +36,18 @@
 //                read from shared memory once), the assign warps add the two halves
 //   warps 2-5    row norms ||x||^2 and ||x - x^||^2 on the first pass of a fit; later passes read them back and
 //                these warps are four more update warps
-//   warps 6-13   assign, two groups taking alternate tiles: tcgen05.ld, three smallest scores by a tournament,
-//                verdict, label masks (shared-memory atomic OR: order-free)
-//   warps 14-21  update: a warp owns <= 4 labels, lane = float4 column chunk
-// What bounds the kernel is how long a tile occupies its shared-memory stage (3 stages at d = 100): every role is a
-// short dependent instruction stream, so the code is kept small (the roles share a 32 KB instruction cache: an
-// unrolled variant that doubled the code ran at 82 % hit rate and 1.7x the time) and the hand-overs few.
+//   warps 6-13   assign, two groups taking alternate tiles: tcgen05.ld of the real columns only (16 + 8 + 4 column
+//                chunks), three smallest keys by a tournament, verdict, label masks, row list
+//   warps 14-21  update: a warp owns <= 4 labels, lane = float4 column chunk; four list entries per broadcast load,
+//                rows past a run's end are not loaded
+// What the kernel runs out of (B200, d = 100, k = 20): a tile occupies its 52 KB stage for ~9000 cycles (three stages:
+// 2 stages cost +32 % time), the shared-memory pipe is ~70 % busy (TMA writes + tensor-core operand reads + the
+// update warps' row reads), and every role is a short dependent instruction stream.  What paid: fewer instructions
+// on the assign warps (atomic-OR masks instead of a sort, only the real columns, keys without the row norm), fewer
+// shared-memory wavefronts in the update warps, a small code footprint (the roles share a 32 KB instruction cache:
+// an unrolled variant that doubled the code ran at 82 % hit rate and 1.7x the time).  What did not: starting the
+// MMAs before the whole tile has landed, an L2 prefetch ahead of the TMA loads, both assign groups on one tile,
+// two labels per update loop, inline waits everywhere.
 //
 // Replaces cuML's fusedL2NN + reduce_rows_by_key pair behind reference
 // python/src/spark_rapids_ml/clustering.py:367-370 (fit) and :493-497 (predict).
@@ -705,8 +712,8 @@ __global__ void __launch_bounds__(kThreads, 1)
             const bool amb = (valid && p.k > 1 && !pair_ok) || third;
             verdict = (unsigned)i1 | ((unsigned)i2 << 8) | (amb ? kInfoUnsafe | (third ? kInfoReach : kInfoPair) : 0u);
 
-            // the verdict goes out with the row; unsafe rows keep the computed best as a provisional label (also in
-            // the sums) until screen_fixup_kernel has decided them exactly
+            // open rows leave their verdict word and keep the computed best as a provisional label until the exact
+            // pass has decided them (they are not part of this kernel's sums)
             if (valid) {
                 if (amb) p.info[grow] = verdict;
                 if (p.labels) p.labels[grow] = label;
@@ -719,10 +726,8 @@ __global__ void __launch_bounds__(kThreads, 1)
             if (et == 0) trace_ev(p, it, 5);
 
             if (p.acc) {
-                // ---- which rows go to which label: one mask word per (label, warp) ----
-                // Rows that are open (the exact pass adds them) or past the end take no part.  The update warps
-                // turn the masks of the labels they own into row lists themselves: no barrier among the assign
-                // warps, no sorted permutation to hand over.
+                // ---- which rows go to which label: one mask word per (label, warp), then the row list ----
+                // Rows that are open (the exact pass adds them) or past the end take no part.
                 sc_wait(s_empty0 + 8u * sb, (uint32_t)(((it >> 1) & 1) ^ 1));
                 const int bin = (valid && !amb) ? label : -1;
                 // every row ORs its bit into its label's word (order does not matter for an OR)
