@@ -30,6 +30,11 @@ def build(verbose=False, force=False):
     os.makedirs(LIBDIR, exist_ok=True)
     headers = [os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith((".cuh", ".h"))]
     headers.append(os.path.join(HERE, "..", "include", "b200km.h"))
+    # objects built with other flags (a development build with B200KM_ENABLE_TRACE ...) are not reused
+    stamp = os.path.join(LIBDIR, ".flags")
+    flags = " ".join(NVCC_FLAGS)
+    if not os.path.exists(stamp) or open(stamp).read() != flags:
+        force = True
     objs = []
     for src in SOURCES:
         path = os.path.join(CSRC, src)
@@ -45,6 +50,8 @@ def build(verbose=False, force=False):
         if verbose:
             print(" ".join(cmd))
         subprocess.check_call(cmd)
+    with open(stamp, "w") as f:
+        f.write(flags)
     return LIB
 
 
