@@ -3,8 +3,8 @@
 //
 // The open rows (C2: ~1 % of the rows, scattered) come out of the bitmap as ONE list in row order:
 //   open_count  popcount of every block of 2048 bitmap words
-//   open_scan   exclusive prefix of the block counts, the total
-//   open_list   (row index, verdict word) of every open row at its position
+//   open_list   every block adds up the counts before it (and the total), then writes (row index, verdict word) of
+//               its open rows at their positions; beyond 4096 blocks open_scan does the prefix in a launch of its own
 // and persistent CTAs walk the list 64 rows at a time in a fixed assignment (CTA c takes batches c, c + grid, ...):
 // the batch's rows are fetched into shared memory all at once (one HBM latency for 64 scattered rows instead of one
 // per row), decided there by groups of 16 lanes, and added - thread t owns column t, rows in list order - into the
@@ -218,15 +218,55 @@ __global__ void __launch_bounds__(1024) open_scan_kernel(unsigned int* __restric
     }
 }
 
+// scanned: blk holds the exclusive prefixes and *total is set (open_scan_kernel ran: very many blocks); otherwise blk
+// holds the block counts and every block adds up its own prefix and the total (a few hundred values).
 __global__ void __launch_bounds__(256) open_list_kernel(const unsigned int* __restrict__ bits, int64_t n_words,
-                                                        const unsigned int* __restrict__ blk,
+                                                        const unsigned int* __restrict__ blk, int n_blk, int scanned,
                                                         const unsigned int* __restrict__ info,
-                                                        const unsigned long long* __restrict__ total,
-                                                        unsigned long long cap, long long* __restrict__ rows,
-                                                        unsigned int* __restrict__ words) {
+                                                        unsigned long long* __restrict__ total, unsigned long long cap,
+                                                        long long* __restrict__ rows, unsigned int* __restrict__ words,
+                                                        IterState* st, int honor_done) {
     __shared__ unsigned int s_warp[8];
-    if (*total > cap) return;  // the tile-range kernel does the work
+    __shared__ unsigned long long s_sum[2][8];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    unsigned long long before, all;
+    if (scanned) {
+        all = *total;
+        before = blk[blockIdx.x];
+    } else {
+        if (honor_done && st->done) {  // the screen kernel did not run: the bitmap is the previous pass's
+            if (blockIdx.x == 0 && tid == 0) *total = 0ull;
+            return;
+        }
+        unsigned long long b = 0ull, a = 0ull;
+        for (int j = tid; j < n_blk; j += 256) {
+            const unsigned int v = blk[j];
+            a += v;
+            if (j < (int)blockIdx.x) b += v;
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            a += __shfl_xor_sync(0xffffffffu, a, o);
+            b += __shfl_xor_sync(0xffffffffu, b, o);
+        }
+        if (lane == 0) {
+            s_sum[0][warp] = a;
+            s_sum[1][warp] = b;
+        }
+        __syncthreads();
+        all = 0ull;
+        before = 0ull;
+#pragma unroll
+        for (int q = 0; q < 8; ++q) {
+            all += s_sum[0][q];
+            before += s_sum[1][q];
+        }
+        if (blockIdx.x == 0 && tid == 0) {
+            *total = all;
+            st->screen_refined += (unsigned int)min(all, 0xffffffffull);
+        }
+    }
+    if (all > cap) return;  // the tile-range kernel does the work
     const int64_t w0 = (int64_t)blockIdx.x * kWordsPerBlock + (int64_t)tid * 8;
     unsigned int w[8];
     unsigned int c = 0;
@@ -243,7 +283,7 @@ __global__ void __launch_bounds__(256) open_list_kernel(const unsigned int* __re
     }
     if (lane == 31) s_warp[warp] = incl;
     __syncthreads();
-    unsigned int off = blk[blockIdx.x] + incl - c;
+    unsigned int off = (unsigned int)before + incl - c;
     for (int q = 0; q < warp; ++q) off += s_warp[q];
 #pragma unroll
     for (int i = 0; i < 8; ++i) {
@@ -500,21 +540,30 @@ __global__ void __launch_bounds__(256) screen_fixup_kernel(const float* __restri
     }
 }
 
-// acc[i] += sum over the slots of slot[i], in slot order: one warp per element, lane l adds slots l, l+32, ... and
-// the lanes meet in a fixed tree.
+// acc[i] += sum over the slots of slot[i] in a fixed order.  A block takes 32 consecutive elements (a warp reads
+// 256 contiguous bytes of a slot); warp g adds the slots g, g + 8, ... in ascending order and the eight partial sums
+// of an element are added in warp order.
 __global__ void __launch_bounds__(256) slot_reduce_kernel(const double* __restrict__ slots, int nslots, int slot_stride,
                                                           int len, double* __restrict__ acc, IterState* st, int honor_done) {
+    __shared__ double part[8][32];
     if (honor_done && st->done) return;
-    const int lane = threadIdx.x & 31;
-    const int i = blockIdx.x * 8 + (threadIdx.x >> 5);
-    if (i >= len) return;
+    const int e = threadIdx.x & 31, g = threadIdx.x >> 5;
+    const int i = blockIdx.x * 32 + e;
     double t = 0.0;
-    for (int sidx = lane; sidx < nslots; sidx += 32) t += slots[(size_t)sidx * slot_stride + i];
+    if (i < len) {
+        const double* src = slots + i;
+#pragma unroll 8
+        for (int sidx = g; sidx < nslots; sidx += 8) t += src[(size_t)sidx * slot_stride];
+    }
+    part[g][e] = t;
+    __syncthreads();
+    if (g == 0 && i < len) {
+        double sum = part[0][e];
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) t += __shfl_down_sync(0xffffffffu, t, o);
-    if (lane == 0) acc[i] += t;
+        for (int q = 1; q < 8; ++q) sum += part[q][e];
+        acc[i] += sum;
+    }
 }
-
 
 }  // namespace
 
@@ -566,10 +615,13 @@ int screen_fixup(TcWorkspace* ws, const float* X, int64_t n, int d, int k, const
 
     open_count_kernel<<<n_blk, 256, 0, s>>>(bits, n_words, blk);
     count_launch();
-    open_scan_kernel<<<1, 1024, 0, s>>>(blk, n_blk, total, st, hd & 1);
-    count_launch();
-    open_list_kernel<<<n_blk, 256, 0, s>>>(bits, n_words, blk, info, total, (unsigned long long)cap,
-                                           (long long*)ws->d_open_rows, (unsigned int*)ws->d_open_info);
+    const int scanned = n_blk > 4096 ? 1 : 0;  // (more than 268M rows)
+    if (scanned) {
+        open_scan_kernel<<<1, 1024, 0, s>>>(blk, n_blk, total, st, hd & 1);
+        count_launch();
+    }
+    open_list_kernel<<<n_blk, 256, 0, s>>>(bits, n_words, blk, n_blk, scanned, info, total, (unsigned long long)cap,
+                                           (long long*)ws->d_open_rows, (unsigned int*)ws->d_open_info, st, hd & 1);
     count_launch();
     {
         // rows of a batch: 64, fewer when d is large (the batch sits in shared memory next to the float64 partial)
@@ -602,7 +654,7 @@ int screen_fixup(TcWorkspace* ws, const float* X, int64_t n, int d, int k, const
         count_launch();
     }
     if (acc) {
-        slot_reduce_kernel<<<(acc_n + 1 + 7) / 8, 256, 0, s>>>((const double*)ws->d_slots, screen_slots + fix_grid,
+        slot_reduce_kernel<<<(acc_n + 1 + 31) / 32, 256, 0, s>>>((const double*)ws->d_slots, screen_slots + fix_grid,
                                                               slot_stride, acc_n + 1, acc, st, hd & 1);
         count_launch();
     }
