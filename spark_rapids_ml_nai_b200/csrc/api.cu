@@ -721,6 +721,9 @@ int b200km_query_workspace(int64_t n, int d, int k, size_t* bytes_out) {
     size_t b = sizeof(double) * (kd + k + 1 + 64) + sizeof(double) * (k + 64) + sizeof(float) * (k + 64) +
                sizeof(float) * (kd + kd / 8 + 64) + 16 * ((size_t)n + (size_t)n / 8 + 256) + sizeof(IterState);
     b += tc_workspace_bytes(d, k) > screen_workspace_bytes(d, k) ? tc_workspace_bytes(d, k) : screen_workspace_bytes(d, k);
+    // fused small-k path: per-CTA partial-sum slots and the fixed part of the open-row list (its per-row part, the
+    // bitmap and the block counts are within the per-row slack above)
+    b += sizeof(double) * (kd + k + 9) * (size_t)(kNumSMs * (1 + kFixCtasPerSm)) + 12 * 65536 + 4096;
     if (!tc_supported(nullptr, d, k, true)) b += gemm_workspace_bytes(n, d, k);
     *bytes_out = b;
     return 0;
