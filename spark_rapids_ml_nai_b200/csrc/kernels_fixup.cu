@@ -609,7 +609,10 @@ int screen_fixup(TcWorkspace* ws, const float* X, int64_t n, int d, int k, const
 #ifdef B200KM_ENABLE_TRACE
     if (const char* e = getenv("B200KM_FIXSKIP")) hd |= atoi(e) << 1;
 #endif
-    const int fix_grid = kNumSMs * kFixCtasPerSm;
+    // CTAs (= partial-sum slots) of the exact pass: all that fit for a large shard, fewer for a small one (every slot
+    // costs a write here and a read in the slot reduction; a small shard has few open rows)
+    int fix_grid = (int)(n / 16384 < kNumSMs * kFixCtasPerSm ? n / 16384 : kNumSMs * kFixCtasPerSm);
+    if (fix_grid < kNumSMs) fix_grid = kNumSMs;
     double* fix_slots = acc ? (double*)ws->d_slots + (size_t)screen_slots * slot_stride : nullptr;
     const int acc_n = k * d + k;
 
