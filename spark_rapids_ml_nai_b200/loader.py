@@ -17,7 +17,9 @@ import os
 _STAGE_BYTES = int(os.environ.get("B200KM_STAGE_MB", "128")) << 20  # one pinned staging slot
 # worker threads of the pageable -> pinned copies: the staging copy is what a fit from host batches waits for
 # (B200 box, 16 cores, 20 GB: 4 threads 1.04 s, 8 threads 0.86 s, 16 threads 0.77 s)
-_COPY_THREADS = int(os.environ.get("B200KM_COPY_THREADS", str(min(16, os.cpu_count() or 8))))
+# The cores are shared by the ranks of a node (torchrun sets LOCAL_WORLD_SIZE).
+_COPY_THREADS = int(os.environ.get("B200KM_COPY_THREADS", "0")) or max(
+    4, min(16, (os.cpu_count() or 8) // max(1, int(os.environ.get("LOCAL_WORLD_SIZE", "1")))))
 _staging = {}
 _pool = None
 
