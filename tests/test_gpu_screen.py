@@ -62,6 +62,22 @@ def test_structureless_data_is_still_exact(handle, n, d, k):
     assert open_rows < n
 
 
+def test_more_open_rows_than_the_list_holds(handle):
+    """The exact pass walks a list of the open rows that holds n/16 + 65536 entries; beyond that (data the screen
+    cannot decide: one blob shared by three nearly identical centroids) the tile-range kernel does the same work
+    straight from the bitmap.  Labels, counts and sums are exact either way."""
+    rng = np.random.default_rng(23)
+    n, d = 400_000, 64
+    centre = np.full(d, 40.0, dtype=np.float32)
+    X = (centre + rng.standard_normal((n, d))).astype(np.float32)
+    C = np.stack([centre, centre + np.float32(1e-3), centre - np.float32(1e-3), centre - 30.0]).astype(np.float32)
+    open_rows = _check_step(handle, X, C, expect_open=True)
+    assert open_rows > n // 16 + 65536
+    labels, _ = handle.predict(dev(X), dev(C))  # the labels-only pass takes the same route
+    l_ref, best, second = ko.assign(X, C)
+    parity.assert_labels_match(labels.cpu().numpy(), best, second, l_ref)
+
+
 def test_close_centroids_far_from_origin(handle):
     # three centroids 1e-3 apart inside one blob 40 units from the origin: every row of the blob stays open
     # (pair and third-candidate tests fail) and only the exact pass can separate them
