@@ -380,7 +380,8 @@ __global__ void __launch_bounds__(kThreads, 1)
     // columns (the tile is read from shared memory once, the assign warps add the two halves); otherwise two
     // instructions per K-step into the same k_pad columns.
     const bool stacked = p.stacked != 0;
-    const int dcols = stacked ? 2 * p.k_pad : p.k_pad;
+    const int dcols = stacked ? 2 * p.k_pad : p.k_pad;   // N of the MMA
+    const int dstride = (dcols + 31) & ~31;              // TMEM columns from one score buffer to the next
     const int n_groups = p.acc ? 2 : 4;  // assign groups: without an update stage its warps score tiles too
     // update warps: 14-21, and - on passes that read the row norms back - the four idle norm warps as well
     const int n_upd = p.xn_compute ? kOwnBinsFirst : kOwnBinsLater;
@@ -541,7 +542,7 @@ __global__ void __launch_bounds__(kThreads, 1)
             mbar_wait(x_full0 + 8u * s, sph);
             tc_fence_after();
             if (lane == 0) trace_ev(p, it, 1);
-            const uint32_t d_tmem = tmem_base + (uint32_t)(db * dcols);
+            const uint32_t d_tmem = tmem_base + (uint32_t)(db * dstride);
             const uint64_t soff = (uint64_t)((s * stage_bytes) >> 4);
             if (elect_one()) {
                 uint64_t ad = adesc_full + soff, bd = bdesc_full;
@@ -654,7 +655,7 @@ __global__ void __launch_bounds__(kThreads, 1)
             tc_fence_after();
             if (et == 0) trace_ev(p, it, 4);
 
-            const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(db * dcols);
+            const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(db * dstride);
             int label = 0;
             unsigned int verdict = 0;  // this row's info word
             // ---- the scores a chunk of columns at a time into registers (score_chunk) ----
@@ -918,7 +919,7 @@ Plan make_plan(int d, int k, bool with_acc) {
     pl.ok = false;
     if (d <= 0 || k <= 0 || d > kMaxD || k > kMaxK || (d & 3)) return pl;
     if (with_acc && (d > 128 || k > kMaxKAcc)) return pl;  // update warps: lane = float4 column chunk, <= 4 labels each
-    pl.k_pad = (k + 31) & ~31;  // the assign warps take the scores 32 at a time
+    pl.k_pad = (k + 15) & ~15;  // N of the MMA (M = 128: a multiple of 16); the assign warps read the real columns
     // K-atoms: 32-float SWIZZLE_128B atoms, and a narrow SWIZZLE_32B / 64B tail when d % 32 is in 4..16
     const int rem = d & 31;
     pl.n_full = d >> 5;
